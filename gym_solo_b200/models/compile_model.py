@@ -1,0 +1,324 @@
+"""URDF + STL -> compiled Solo model blob (JSON).
+
+Offline tool.  Reads a Solo URDF and its collision
+meshes and writes the constant model blob that the CUDA path and the CPU oracle
+both consume through ``SoloModel`` (include/solo8_b200.h).  The blob is
+committed; the URDF/STL sources are not (they stay in the reference tree:
+gym_solo/assets/solo8v2/solo.urdf:8-583, gym_solo/assets/solo8_URDF_v4/*.urdf).
+
+What it mirrors of pybullet's URDF import (Bullet recollection):
+  * link/joint flattening order = depth-first from the base, children in file
+    order -> pybullet joint index (golden: test_obs_observations.py:237-239);
+  * ``URDF_USE_INERTIA_FROM_FILE``: mass / COM / inertia tensor from <inertial>;
+    the *base* frame that the getters report is the base inertial frame (COM,
+    principal axes), so the base body is re-expressed in that frame;
+  * fixed joints carry no dof: the child is merged into its dynamic parent
+    (rigidly equivalent); its API slot stays (12-wide API, reads 0.0);
+  * collision mesh -> convex hull, 1 mm outward margin (btConvexHullShape).
+
+Collision reduction (ours): each hull is reduced to a small support-point set
+(box-corner directions in extent-scaled space; knee-end points for the lower
+leg; 8 rim points of the foot disc) because the ground is the plane z = 0 and a
+convex hull touches a plane at its support point in the -n direction.
+
+usage: python -m gym_solo_b200.models.compile_model <urdf> <out.json> [--name N]
+"""
+import json
+import math
+import os
+import struct
+import sys
+import xml.etree.ElementTree as ET
+
+import numpy as np
+
+MAX_LEGS = 4
+MAX_CHAIN = 3
+
+
+def rpy_to_mat(r, p, y):
+  cr, sr, cp, sp, cy, sy = (math.cos(r), math.sin(r), math.cos(p), math.sin(p),
+                            math.cos(y), math.sin(y))
+  return np.array([[cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr],
+                   [sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr],
+                   [-sp, cp * sr, cp * cr]])
+
+
+def read_stl(path):
+  d = open(path, 'rb').read()
+  n = struct.unpack('<I', d[80:84])[0]
+  if 84 + 50 * n != len(d):
+    raise ValueError('only binary STL supported: ' + path)
+  rec = np.dtype([('n', '<f4', 3), ('v', '<f4', (3, 3)), ('a', '<u2')])
+  a = np.frombuffer(d, dtype=rec, count=n, offset=84)
+  return np.unique(a['v'].reshape(-1, 3).astype(np.float64), axis=0)
+
+
+def _floats(s, n):
+  v = [float(x) for x in s.split()]
+  assert len(v) == n, s
+  return v
+
+
+def _origin(el):
+  o = el.find('origin') if el is not None else None
+  if o is None:
+    return np.zeros(3), np.eye(3)
+  xyz = np.array(_floats(o.get('xyz', '0 0 0'), 3))
+  rpy = _floats(o.get('rpy', '0 0 0'), 3)
+  return xyz, rpy_to_mat(*rpy)
+
+
+def parse_urdf(path):
+  root = ET.parse(path).getroot()
+  links, joints = {}, []
+  for l in root.findall('link'):
+    inert = l.find('inertial')
+    com, Rin = _origin(inert)
+    mass = float(inert.find('mass').get('value'))
+    i = inert.find('inertia')
+    g = lambda k: float(i.get(k, '0'))
+    I = np.array([[g('ixx'), g('ixy'), g('ixz')],
+                  [g('ixy'), g('iyy'), g('iyz')],
+                  [g('ixz'), g('iyz'), g('izz')]])
+    I = Rin @ I @ Rin.T          # inertia in link-frame axes
+    col = l.find('collision')
+    mesh, cxyz, cR = None, np.zeros(3), np.eye(3)
+    if col is not None:
+      cxyz, cR = _origin(col)
+      m = col.find('geometry').find('mesh')
+      if m is not None:
+        mesh = m.get('filename')
+    c = l.find('contact')
+    mu = 0.5  # Bullet's default lateral friction when no <contact> tag
+    if c is not None and c.find('lateral_friction') is not None:
+      mu = float(c.find('lateral_friction').get('value'))
+    links[l.get('name')] = dict(name=l.get('name'), mass=mass, com=com, I=I,
+                                mesh=mesh, cxyz=cxyz, cR=cR, mu=mu)
+  for j in root.findall('joint'):
+    xyz, R = _origin(j)
+    ax = j.find('axis')
+    axis = np.array(_floats(ax.get('xyz'), 3)) if ax is not None else np.array([1., 0, 0])
+    lim = j.find('limit')
+    lo = float(lim.get('lower', '0')) if lim is not None else 0.
+    hi = float(lim.get('upper', '0')) if lim is not None else 0.
+    joints.append(dict(name=j.get('name'), type=j.get('type'),
+                       parent=j.find('parent').get('link'),
+                       child=j.find('child').get('link'),
+                       xyz=xyz, R=R, axis=axis, lower=lo, upper=hi))
+  children = {n: [] for n in links}
+  has_parent = set()
+  for j in joints:
+    children[j['parent']].append(j)
+    has_parent.add(j['child'])
+  base = [n for n in links if n not in has_parent]
+  assert len(base) == 1
+  return links, joints, children, base[0]
+
+
+def support_points(hv, kind):
+  """Reduce hull vertices to the support set used against the ground plane."""
+  lo, hi = hv.min(0), hv.max(0)
+  ext = np.maximum(hi - lo, 1e-9)
+  mid = 0.5 * (lo + hi)
+  pts = []
+  if kind in ('box8', 'top4'):
+    for sx in (-1, 1):
+      for sy in (-1, 1):
+        for sz in ((1,) if kind == 'top4' else (-1, 1)):
+          d = np.array([sx, sy, sz]) / ext
+          if kind == 'top4':
+            # knee end only: restrict to the upper half of the link
+            cand = hv[hv[:, 2] > mid[2]]
+          else:
+            cand = hv
+          pts.append(cand[(cand @ d).argmax()])
+  elif kind == 'rim8':
+    # disc with axis y: 8 rim directions in the xz plane, at the mid plane
+    for k in range(8):
+      th = 2 * math.pi * k / 8
+      d = np.array([math.cos(th), 0., math.sin(th)])
+      h = ((hv - mid) @ d).max()
+      pts.append(mid + h * d)
+  else:
+    raise ValueError(kind)
+  return np.array(pts)
+
+
+def link_kind(name):
+  n = name.lower()
+  if 'foot' in n:
+    return 'rim8'
+  if 'lower' in n:
+    return 'top4'
+  return 'box8'
+
+
+def principal_frame(I):
+  """Bullet diagonalises a non-diagonal inertia; returns (diag, R) with
+  I = R diag R^T and R the rotation closest to identity (axes not sorted)."""
+  off = abs(I[0, 1]) + abs(I[0, 2]) + abs(I[1, 2])
+  if off == 0.0:
+    return np.diag(I).copy(), np.eye(3)
+  w, V = np.linalg.eigh(I)
+  # assign eigenvectors to the axis they are most aligned with
+  cols = []
+  remaining = list(range(3))
+  for axis in range(3):
+    k = max(remaining, key=lambda c: abs(V[axis, c]))
+    remaining.remove(k)
+    v = V[:, k] * (1 if V[axis, k] >= 0 else -1)
+    cols.append((w[k], v))
+  R = np.stack([c[1] for c in cols], axis=1)
+  if np.linalg.det(R) < 0:
+    R[:, 2] *= -1
+  return np.array([c[0] for c in cols]), R
+
+
+def compile_model(urdf_path, name=None, fallback_boxes=None):
+  links, joints, children, base = parse_urdf(urdf_path)
+  mesh_dir = os.path.dirname(urdf_path)
+  fallback_boxes = fallback_boxes or {}
+
+  # ---- flatten (DFS, file order) -> pybullet joint indices -------------------
+  api = []          # list of joints in pybullet index order
+
+  def dfs(link):
+    for j in children[link]:
+      api.append(j)
+      dfs(j['child'])
+  dfs(base)
+
+  # ---- base body in its inertial (COM, principal) frame ----------------------
+  bl = links[base]
+  Ib_diag, Rb = principal_frame(bl['I'])
+  # X_base maps URDF-base-link coords -> base-body coords: p_body = Rb^T (p - com)
+  base_com = bl['com'].copy()
+
+  bodies = []       # dynamic bodies: dict(mass, com, I, parts=[(link, p, R)])
+  # each "part" = original link rigidly attached: offset p, rotation R of the
+  # link frame expressed in the body frame
+  bodies.append(dict(name=base, mass=0., com=np.zeros(3), I=np.zeros((3, 3)),
+                     parts=[]))
+
+  legs = []         # list of lists of dof dicts
+
+  def attach(body, link, p, R):
+    """Rigidly add `link` (frame at p,R in body coords) to `body`."""
+    body['parts'].append((link, p, R))
+    for j in children[link]:
+      if j['type'] == 'fixed':
+        attach(body, j['child'], p + R @ j['xyz'], R @ j['R'])
+
+  def merge_inertia(body):
+    m = sum(links[l]['mass'] for l, _, _ in body['parts'])
+    com = sum(links[l]['mass'] * (p + R @ links[l]['com'])
+              for l, p, R in body['parts']) / m
+    I = np.zeros((3, 3))
+    for l, p, R in body['parts']:
+      L = links[l]
+      d = p + R @ L['com'] - com
+      I += R @ L['I'] @ R.T + L['mass'] * (d @ d * np.eye(3) - np.outer(d, d))
+    body.update(mass=m, com=com, I=I)
+
+  attach(bodies[0], base, -Rb.T @ base_com, Rb.T)
+  merge_inertia(bodies[0])
+
+  dof_of_joint = {}
+
+  def walk_chain(parent_body_idx, link, p, R, chain):
+    """Follow movable joints below `link` (frame p,R in parent body coords)."""
+    for j in children[link]:
+      jp, jR = p + R @ j['xyz'], R @ j['R']
+      if j['type'] == 'fixed':
+        walk_chain(parent_body_idx, j['child'], jp, jR, chain)
+        continue
+      if j['type'] not in ('revolute', 'continuous'):
+        raise ValueError('unsupported joint type ' + j['type'])
+      if parent_body_idx == 0:
+        chain = []
+        legs.append(chain)
+      body = dict(name=j['child'], mass=0., com=np.zeros(3), I=np.zeros((3, 3)),
+                  parts=[])
+      attach(body, j['child'], np.zeros(3), np.eye(3))
+      merge_inertia(body)
+      bodies.append(body)
+      idx = len(bodies) - 1
+      ax = j['axis'] / np.linalg.norm(j['axis'])
+      chain.append(dict(joint=j, body=idx, parent=parent_body_idx,
+                        origin=jp, rot=jR, axis=ax))
+      dof_of_joint[j['name']] = idx - 1
+      walk_chain(idx, j['child'], np.zeros(3), np.eye(3), chain)
+
+  walk_chain(0, base, -Rb.T @ base_com, Rb.T, None)
+  assert len(legs) <= MAX_LEGS and all(len(c) <= MAX_CHAIN for c in legs)
+  # dof order must be chain-contiguous
+  d = 0
+  for c in legs:
+    for e in c:
+      assert e['body'] == d + 1, 'dof order is not chain-contiguous'
+      d += 1
+  ndof = d
+
+  # ---- collision support points ---------------------------------------------
+  cand_body, cand_pos, cand_mu, cand_link = [], [], [], []
+  hull_cache = {}
+  for bi, body in enumerate(bodies):
+    for l, p, R in body['parts']:
+      L = links[l]
+      pts = None
+      if L['mesh'] is not None:
+        mp = os.path.join(mesh_dir, L['mesh'])
+        if os.path.exists(mp):
+          if mp not in hull_cache:
+            from scipy.spatial import ConvexHull
+            v = read_stl(mp)
+            hull_cache[mp] = v[ConvexHull(v).vertices]
+          pts = support_points(hull_cache[mp], link_kind(l))
+      if pts is None and l in fallback_boxes:
+        lo, hi = fallback_boxes[l]
+        pts = np.array([[x, y, z] for x in (lo[0], hi[0]) for y in (lo[1], hi[1])
+                        for z in (lo[2], hi[2])])
+      if pts is None:
+        continue
+      for q in pts:
+        q_link = L['cxyz'] + L['cR'] @ q
+        cand_body.append(bi)
+        cand_pos.append((p + R @ q_link).tolist())
+        cand_mu.append(L['mu'])
+        cand_link.append(l)
+
+  model = dict(
+      name=name or os.path.splitext(os.path.basename(urdf_path))[0],
+      source=os.path.relpath(urdf_path, '/root/reference'),
+      n_legs=len(legs), chain_len=[len(c) for c in legs], ndof=ndof,
+      n_api=len(api), api_names=[j['name'] for j in api],
+      api_dof=[dof_of_joint.get(j['name'], -1) for j in api],
+      api_lower=[j['lower'] for j in api], api_upper=[j['upper'] for j in api],
+      body_names=[b['name'] for b in bodies],
+      body_mass=[b['mass'] for b in bodies],
+      body_com=[b['com'].tolist() for b in bodies],
+      body_inertia=[b['I'].tolist() for b in bodies],
+      joint_parent=[e['parent'] for c in legs for e in c],
+      joint_origin=[e['origin'].tolist() for c in legs for e in c],
+      joint_rot=[e['rot'].tolist() for c in legs for e in c],
+      joint_axis=[e['axis'].tolist() for c in legs for e in c],
+      base_inertial_pos=base_com.tolist(), base_inertial_rot=Rb.tolist(),
+      n_cand=len(cand_body), cand_body=cand_body, cand_pos=cand_pos,
+      cand_mu=cand_mu, cand_link=cand_link, collision_margin=0.001,
+  )
+  return model
+
+
+def main(argv):
+  urdf, out = argv[1], argv[2]
+  name = argv[argv.index('--name') + 1] if '--name' in argv else None
+  m = compile_model(urdf, name)
+  with open(out, 'w') as f:
+    json.dump(m, f, indent=1)
+  print('wrote', out, 'ndof', m['ndof'], 'bodies', len(m['body_mass']),
+        'cands', m['n_cand'], 'mass', sum(m['body_mass']))
+
+
+if __name__ == '__main__':
+  main(sys.argv)

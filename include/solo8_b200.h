@@ -1,0 +1,219 @@
+/* solo8_b200.h -- C-ABI of the B200-native batched Solo 8 step path.
+ *
+ * Drop-in boundary.  The reference has no FFI: its
+ * boundary is the set of pybullet BulletClient calls made by
+ *   gym_solo/envs/solo8v2vanilla.py:72-102   (step)
+ *   gym_solo/envs/solo8v2vanilla.py:104-143  (reset, 500 settle steps)
+ *   gym_solo/core/obs.py:130-159, 260-282, 347-363      (observations)
+ *   gym_solo/core/rewards.py:104-118, 221-234, 237-373  (rewards)
+ *   gym_solo/core/termination.py:38-56, 59-98           (terminations)
+ * Each entry point below names the reference call(s) it replaces.  Plain C
+ * types only: pointers, sizes, PODs.  Every `*_dev` pointer is CUDA device
+ * memory owned by the caller (PyTorch tensors in the Python host layer); the
+ * handle owns only the constant model / config / program tables.
+ *
+ * All functions return 0 on success, a negative SOLO_E* code otherwise;
+ * solo_last_error() gives the message.  Calls on one handle are stream
+ * ordered and not thread-safe (one handle per process per GPU).
+ */
+#ifndef SOLO8_B200_H_
+#define SOLO8_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SOLO_MAX_LEGS 4
+#define SOLO_MAX_CHAIN 3
+#define SOLO_MAX_DOF 12
+#define SOLO_MAX_BODIES 13
+#define SOLO_MAX_API 16
+#define SOLO_MAX_CAND 128
+#define SOLO_MAX_OBS_TERMS 8
+#define SOLO_MAX_REWARD_OPS 32
+#define SOLO_MAX_TERM_TERMS 8
+#define SOLO_REWARD_STACK 8
+
+#define SOLO_OK 0
+#define SOLO_EINVAL (-1)
+#define SOLO_ECUDA (-2)
+#define SOLO_ENOGPU (-3)
+
+/* Compiled robot model (written by gym_solo_b200/models/compile_model.py from
+ * gym_solo/assets/solo8v2/solo.urdf:8-583).  Body 0 is the floating base in
+ * its inertial frame; body 1+d is the child of dof d.  Dofs are chain
+ * contiguous: leg l owns dofs [sum(chain_len[:l]), +chain_len[l]). */
+typedef struct SoloModel {
+  int32_t n_legs, ndof, n_api, n_cand;
+  int32_t chain_len[SOLO_MAX_LEGS];
+  int32_t api_dof[SOLO_MAX_API];          /* pybullet joint index -> dof, -1 = fixed */
+  double api_lower[SOLO_MAX_API], api_upper[SOLO_MAX_API];
+  double body_mass[SOLO_MAX_BODIES];
+  double body_com[SOLO_MAX_BODIES][3];      /* in body frame */
+  double body_inertia[SOLO_MAX_BODIES][9];  /* about COM, body-frame axes */
+  double joint_origin[SOLO_MAX_DOF][3];     /* joint frame origin in parent body frame */
+  double joint_rot[SOLO_MAX_DOF][9];        /* parent<-child rotation at q = 0 */
+  double joint_axis[SOLO_MAX_DOF][3];       /* unit axis in child frame */
+  int32_t cand_body[SOLO_MAX_CAND];         /* contact support points, grouped by body */
+  double cand_pos[SOLO_MAX_CAND][3];        /* in body frame */
+  double cand_mu[SOLO_MAX_CAND];            /* link lateral friction (changeDynamics) */
+  double collision_margin;                  /* 0.001: btConvexHullShape margin */
+} SoloModel;
+
+/* Physics configuration = Solo8BaseConfig (gym_solo/core/configs.py:8-38) plus
+ * the Bullet world defaults pybullet sets (recollection). */
+typedef struct SoloConfig {
+  double dt;                      /* configs.py:10 (1e-3); BASELINE configs use 1/240 */
+  double gravity[3];              /* configs.py:17 */
+  double motor_torque_limit;      /* configs.py:12; max impulse = limit*dt */
+  double linear_damping;          /* configs.py:21 */
+  double angular_damping;         /* configs.py:22 */
+  double plane_friction;          /* pybullet_data plane.urdf: 1.0 */
+  double motor_kp, motor_kd;      /* pybullet POSITION_CONTROL defaults 0.1 / 1.0 */
+  double contact_erp;             /* m_erp2 = 0.08 */
+  double contact_slop;            /* m_linearSlop = 1e-5 */
+  double contact_breaking_threshold; /* 0.02 */
+  double max_coordinate_velocity; /* btMultiBody m_maxCoordinateVelocity = 100 */
+  double residual_threshold;      /* m_leastSquaresResidualThreshold = 1e-7 */
+  int32_t solver_iterations;      /* 50 */
+  int32_t num_substeps;           /* physics steps of dt per action (reference: 1) */
+  int32_t control_mode;           /* 0 = POSITION_CONTROL, 1 = torque */
+  int32_t max_contacts;           /* cap on simultaneous contact points per env */
+} SoloConfig;
+
+#define SOLO_CONTROL_POSITION 0
+#define SOLO_CONTROL_TORQUE 1
+
+/* State layout, structure-of-arrays: state[f * n_envs + env], float32.
+ *   f 0..2 base COM position, 3..6 base quaternion (x,y,z,w), 7..9 base linear
+ *   velocity (world), 10..12 base angular velocity (world), then q[ndof],
+ *   qdot[ndof].  == getBasePositionAndOrientation / getBaseVelocity /
+ *   getJointState of the reference (obs.py:268-273, 354). */
+#define SOLO_STATE_BASE 13
+#define SOLO_STATE_DIM(ndof) (SOLO_STATE_BASE + 2 * (ndof))
+
+/* ---- fused epilogue program ------------------------------------------------ */
+
+/* Observation terms (obs.py:193-363), concatenated in registration order. */
+#define SOLO_OBS_TORSO_IMU 1
+#define SOLO_OBS_MOTOR_ENCODER 2
+typedef struct SoloObsTerm {
+  int32_t kind;
+  int32_t degrees;        /* obs.py:275-279, 357-358 */
+  int32_t clip;           /* MotorEncoder: max_rotation given (obs.py:360-361) */
+  int32_t normalize;      /* ObservationFactory(normalize=True) (obs.py:148-152) */
+  float clip_lo[SOLO_MAX_API], clip_hi[SOLO_MAX_API];   /* np.clip bounds */
+  float norm_lo[SOLO_MAX_API], norm_hi[SOLO_MAX_API];   /* float32 Box low/high */
+} SoloObsTerm;
+
+/* Reward program: postfix (RPN) over a small stack.
+ * RewardFactory.get_reward = sum_i w_i r_i (rewards.py:104-118);
+ * AdditiveReward (rewards.py:121-160); MultiplicitiveReward (rewards.py:163-199). */
+#define SOLO_REW_UPRIGHT 1      /* rewards.py:221-234 */
+#define SOLO_REW_FLAT_TORSO 2   /* rewards.py:237-269: p0 hard, p1 soft */
+#define SOLO_REW_SMALL_CONTROL 3/* rewards.py:272-301: p1 margin */
+#define SOLO_REW_HSPEED 4       /* rewards.py:304-338: p0 lo, p1 hi, p2 margin */
+#define SOLO_REW_HEIGHT 5       /* rewards.py:341-373: p0 lo, p1 hi, p2 margin */
+#define SOLO_REW_CONST 6        /* push p0 */
+#define SOLO_REW_ADD 16         /* pop n, push sum_k c_k * x_k with c in coef[] */
+#define SOLO_REW_MUL 17         /* pop n, push p0 * prod x_k */
+typedef struct SoloRewardOp {
+  int32_t op;
+  int32_t n;              /* arity for ADD / MUL */
+  float p[4];             /* leaf parameters: lower, upper, margin, scale */
+  float coef[SOLO_REWARD_STACK];
+} SoloRewardOp;
+
+/* Termination terms (termination.py:59-98), OR-combined with short circuit. */
+#define SOLO_TERM_PERPETUAL 1
+#define SOLO_TERM_TIME 2        /* max_step_delta; one int32 counter per env */
+typedef struct SoloTermTerm {
+  int32_t kind;
+  int32_t max_step_delta;
+} SoloTermTerm;
+
+typedef struct SoloProgram {
+  int32_t n_obs, n_rew, n_term;
+  int32_t auto_reset;     /* 1: envs that terminate are restored from the snapshot in-kernel */
+  SoloObsTerm obs[SOLO_MAX_OBS_TERMS];
+  SoloRewardOp rew[SOLO_MAX_REWARD_OPS];
+  SoloTermTerm term[SOLO_MAX_TERM_TERMS];
+} SoloProgram;
+
+typedef struct SoloHandle_ *SoloHandle;
+
+/* BulletClient(DIRECT) + setGravity + setPhysicsEngineParameter + loadURDF +
+ * changeDynamics  (solo8_base_env.py:34-48, solo8v2vanilla.py:145-172). */
+int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs,
+                int32_t device, SoloHandle *out);
+/* client.disconnect (solo8_base_env.py:150-152). */
+int solo_destroy(SoloHandle h);
+/* obs_factory.register_observation / reward_factory.register_reward /
+ * termination_factory.register_termination, compiled to tables
+ * (obs.py:109-128, rewards.py:87-102, termination.py:29-36). */
+int solo_set_program(SoloHandle h, const SoloProgram *program);
+/* len(observation_space.low) for the current program (obs.py:161-190). */
+int solo_obs_dim(SoloHandle h);
+/* Bytes of per-env scratch the caller must bind (0 if none). */
+int64_t solo_scratch_bytes(SoloHandle h);
+
+/* Bind caller-owned device buffers.  state_dev: float[SOLO_STATE_DIM][n_envs];
+ * counters_dev: int32[SOLO_MAX_TERM_TERMS][n_envs]; snapshot_dev:
+ * float[SOLO_STATE_DIM] post-reset state (solo8v2vanilla.py:124-136 computed
+ * once); stats_dev: float[4][n_envs] episode return / length / last return /
+ * episodes (may be NULL); scratch_dev: solo_scratch_bytes() bytes (may be NULL
+ * when that is 0). */
+int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev,
+              float *snapshot_dev, float *stats_dev, void *scratch_dev);
+
+/* Physics only: setJointMotorControlArray + stepSimulation
+ * (solo8v2vanilla.py:87-91), `n_steps` times with the same command.
+ * actions_dev: float[n_envs][n_api], or float[n_api] broadcast when
+ * `broadcast` != 0 (the 500 settle steps of reset, solo8v2vanilla.py:130-136). */
+int solo_simulate(SoloHandle h, const float *actions_dev, int32_t broadcast,
+                  int32_t n_steps, void *stream);
+
+/* One env.step for every env (solo8v2vanilla.py:72-102): optional action
+ * scaling `a * action_scale` (normalize_actions, :84-85; pass 1.0f otherwise),
+ * motor command, num_substeps physics steps, observations, reward,
+ * termination, optional in-kernel auto reset.  Outputs: obs_dev
+ * float[n_envs][obs_dim], reward_dev float[n_envs], done_dev uint8[n_envs];
+ * terminal_obs_dev (may be NULL) receives the pre-reset observation when
+ * auto_reset is on. */
+int solo_step(SoloHandle h, const float *actions_dev, float action_scale,
+              float *obs_dev, float *reward_dev, uint8_t *done_dev,
+              float *terminal_obs_dev, void *stream);
+
+/* obs_factory.get_obs() alone (reset's return value, solo8v2vanilla.py:141-143). */
+int solo_observe(SoloHandle h, float *obs_dev, void *stream);
+/* reward_factory.get_reward() alone on the current state. */
+int solo_reward(SoloHandle h, float *reward_dev, void *stream);
+
+/* env.reset (solo8v2vanilla.py:104-143) by snapshot restore.  mask_dev: uint8
+ * per env (NULL = all).  Also termination_factory.reset() (:137). */
+int solo_reset(SoloHandle h, const uint8_t *mask_dev, void *stream);
+
+/* Same as solo_step but with HOST buffers (the reference's calling convention:
+ * numpy in, numpy out): H2D of actions, the step, D2H of obs/reward/done, and a
+ * stream synchronise, through staging buffers bound with solo_bind_staging. */
+int solo_bind_staging(SoloHandle h, float *actions_dev, float *obs_dev,
+                      float *reward_dev, uint8_t *done_dev);
+int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
+                   float *obs_host, float *reward_host, uint8_t *done_host,
+                   void *stream);
+
+/* Diagnostics: per-step solver statistics of the last solo_step/solo_simulate
+ * (sum over envs of contact points, PGS iterations run, NaN resets), written to
+ * a caller device buffer int64[4] when bound (NULL to disable). */
+int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
+/* How many kernels this handle has launched so far (bench `gpu_launches`). */
+int64_t solo_launch_count(SoloHandle h);
+const char *solo_last_error(SoloHandle h);
+const char *solo_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* SOLO8_B200_H_ */
