@@ -1,0 +1,325 @@
+"""bench.py -- Solo8 env-steps/sec on N B200s (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--envs E] [--impl reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one env.step() of every environment of the batch (one fused kernel
+launch per rank).  Workload = BASELINE.json configs[1]: Solo8VanillaEnv, 4096
+envs per GPU, POSITION_CONTROL, flat ground, dt = 1/240, TorsoIMU +
+MotorEncoder observations (21), 1 x UprightReward, PerpetualTermination, fresh
+U(-2pi, 2pi) actions every step (generated on the device outside the timed
+spans).  Weak scaling: every rank owns its own 4096 envs, no data-path
+collective; NCCL only gathers episode statistics after the timed region.
+
+value  = env-steps all ranks processed / max-over-ranks device time (CUDA events
+         around every step on the launching stream; L2 flushed between steps)
+e2e    = the same through Solo8VanillaEnv.step_host (numpy in / numpy out via
+         the C-ABI's solo_step_host: H2D actions + step + D2H obs/reward/done)
+roofline.achieved = 377 algorithmic bytes per env-step x envs per
+         launch / mean launch duration, against the measured HBM copy peak
+cpu_baseline / --impl reference = the double-precision CPU oracle (a port: the
+         reference's own engine, pybullet, is not installable here) on the
+         box's host threads.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+import warnings
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+  sys.path.insert(0, ROOT)
+
+METRIC = 'solo8_env_steps_per_sec'
+UNIT = 'env-steps/s'
+BYTES_PER_ENV_STEP = 377          # 168 B read + 209 B written, float32
+DT = 1.0 / 240.0
+WORKLOAD = ('Solo8VanillaEnv batched 4096 envs on 1xB200, position control, flat-ground contact, '
+            'dt=1/240 (BASELINE.json configs[1])')
+
+
+def parse_args():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--steps', type=int, default=1000)
+  ap.add_argument('--warmup', type=int, default=20)
+  ap.add_argument('--envs', type=int, default=4096, help='environments per GPU')
+  ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+  ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--no-l2-flush', action='store_true')
+  return ap.parse_args()
+
+
+def hbm_peak():
+  p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+  if os.path.exists(p):
+    try:
+      return float(json.load(open(p))['hbm_gbs']), 'measured'
+    except Exception:
+      pass
+  return 6650.0, 'fallback'
+
+
+# ---- clocks under load -------------------------------------------------------------
+class ClockSampler(threading.Thread):
+  REASONS = [(0x8, 'hw_slowdown'), (0x40, 'hw_thermal_slowdown'), (0x20, 'sw_thermal_slowdown'),
+             (0x4, 'sw_power_cap'), (0x80, 'hw_power_brake_slowdown')]
+
+  def __init__(self, index, period=0.02):
+    super().__init__(daemon=True)
+    self.index, self.period = index, period
+    self.samples, self.reasons, self.max_mhz = [], set(), None
+    self._stop = threading.Event()
+    self.recording = False
+    try:
+      import pynvml
+      pynvml.nvmlInit()
+      self.nv = pynvml
+      self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+      self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+    except Exception:
+      self.nv = None
+
+  def run(self):
+    if self.nv is None:
+      return
+    while not self._stop.is_set():
+      if self.recording:
+        try:
+          self.samples.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+          mask = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+          for bit, name in self.REASONS:
+            if mask & bit:
+              self.reasons.add(name)
+        except Exception:
+          pass
+      time.sleep(self.period)
+
+  def stop(self):
+    self._stop.set()
+
+  def summary(self):
+    if not self.samples:
+      return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons), 'samples': 0}
+    return {'sm_mhz': float(np.median(self.samples)), 'sm_max_mhz': self.max_mhz,
+            'reasons': sorted(self.reasons), 'samples': len(self.samples)}
+
+
+# ---- the workload --------------------------------------------------------------------
+def make_env(n_envs, device):
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  cfg = Solo8VanillaConfig()
+  cfg.dt = DT
+  env = Solo8VanillaEnv(config=cfg, num_envs=n_envs, device=device)
+  env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+  env.obs_factory.register_observation(obs.MotorEncoder(env.robot))
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    env.reward_factory.register_reward(1, rewards.UprightReward(env.robot))
+  env.termination_factory.register_termination(termination.PerpetualTermination())
+  env.reset()
+  return env
+
+
+def cpu_oracle_setup():
+  from gym_solo_b200 import _abi
+  from oracle import solo_oracle as so
+  blob = _abi.load_model_blob('solo8v2')
+  model = _abi.make_model(blob, link_friction=0.5)
+  config = _abi.make_config(dt=DT)
+  orc = so.PhysicsOracle(model, config)
+  targets = np.array([np.pi / 2, np.pi, 0, np.pi / 2, np.pi, 0, -np.pi / 2, -np.pi, 0, -np.pi / 2, -np.pi, 0])
+  snap = orc.settle(targets)
+  return so, orc, model, snap
+
+
+def cpu_step(so, orc, model, states, actions, threads):
+  """One env.step of the batch on the host: physics (C, pthreads) + the numpy
+  restatement of get_obs / get_reward / is_terminated."""
+  states = orc.step_batch(states, actions, n_steps=1, n_threads=threads)
+  view = so.StateView(states, model)
+  obs = np.concatenate([so.torso_imu(view)[0], so.motor_encoder(view)[0]], axis=1)
+  rew = so.upright_reward(view)
+  done = np.zeros(states.shape[0], dtype=bool)
+  return states, obs, rew, done
+
+
+def run_cpu(n_envs, steps, warmup, threads, seed=1234):
+  so, orc, model, snap = cpu_oracle_setup()
+  rng = np.random.RandomState(seed)
+  states = np.tile(snap, (n_envs, 1))
+  for _ in range(warmup):
+    states, *_ = cpu_step(so, orc, model, states, rng.uniform(-2 * np.pi, 2 * np.pi, (n_envs, 12)), threads)
+  acts = [rng.uniform(-2 * np.pi, 2 * np.pi, (n_envs, 12)) for _ in range(min(steps, 64))]
+  t0 = time.perf_counter()
+  for k in range(steps):
+    states, *_ = cpu_step(so, orc, model, states, acts[k % len(acts)], threads)
+  dt = time.perf_counter() - t0
+  return n_envs * steps / dt, dt
+
+
+def reference_arm(args, rank):
+  """--impl reference: the CPU path on the host cores.  The reference's engine
+  (pybullet) cannot be installed (no wheel, no network), so this times the
+  oracle port; one step = one env.step of the same 4096-env batch."""
+  if rank != 0:
+    return
+  threads = os.cpu_count() or 1
+  value, total = run_cpu(args.envs, args.steps, min(args.warmup, 3), threads)
+  line = {
+      'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+      'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * total / args.steps,
+      'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+      'data': 'synthetic',
+      'config': {'workload': WORKLOAD, 'envs_per_step': args.envs, 'engine': 'oracle port (C, double)'},
+      'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                       'sample': '%d envs x %d steps, physics on %d pthreads + numpy epilogue'
+                                 % (args.envs, args.steps, threads)},
+      'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+      'gpu_launches': 0,
+  }
+  print(json.dumps(line), flush=True)
+
+
+def main():
+  args = parse_args()
+  rank = int(os.environ.get('RANK', '0'))
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  if args.impl == 'reference':
+    reference_arm(args, rank)
+    return
+
+  import torch
+  import torch.distributed as dist
+  if not torch.cuda.is_available():
+    raise SystemExit('bench.py: no CUDA device; the Solo 8 step path has no CPU fallback')
+  torch.cuda.set_device(local)
+  device = torch.device('cuda', local)
+  if world > 1:
+    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+    dist.init_process_group('nccl', device_id=device)
+
+  n = args.envs
+  env = make_env(n, device)
+  gen = torch.Generator(device=device).manual_seed(1234 + rank)
+  two_pi = float(2 * np.pi)
+
+  def fresh_actions():
+    return (torch.rand((n, 12), generator=gen, device=device) * 2 - 1) * two_pi
+
+  flush = None if args.no_l2_flush else torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)
+  sampler = ClockSampler(local)
+  sampler.start()
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize(device)
+
+  # ---- device-resident arm ------------------------------------------------------------
+  for _ in range(args.warmup):
+    env.step(fresh_actions())
+  barrier()
+  sampler.recording = True
+  launches0 = env.client.launch_count()
+  starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+  ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+  for k in range(args.steps):
+    a = fresh_actions()
+    if flush is not None:
+      flush.fill_(k & 0xff)
+    starts[k].record()
+    env.step(a)
+    ends[k].record()
+  barrier()
+  launches = env.client.launch_count() - launches0
+  per_step_ms = np.array([s.elapsed_time(e) for s, e in zip(starts, ends)])
+  total_ms = float(per_step_ms.sum())
+
+  # ---- end-to-end arm: host buffers through solo_step_host -----------------------------
+  rng = np.random.RandomState(4321 + rank)
+  host_actions = [rng.uniform(-two_pi, two_pi, (n, 12)).astype(np.float32) for _ in range(16)]
+  for k in range(min(args.warmup, 5)):
+    env.step_host(host_actions[k % 16])
+  barrier()
+  e2e_steps = args.steps
+  t0 = time.perf_counter()
+  ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  ev0.record()
+  checksum = 0.0
+  for k in range(e2e_steps):
+    o, r, d, _ = env.step_host(host_actions[k % 16])
+    checksum += float(r[0])
+  ev1.record()
+  barrier()
+  e2e_ms = max(ev0.elapsed_time(ev1), 0.0)
+  e2e_wall_ms = 1e3 * (time.perf_counter() - t0)
+  sampler.recording = False
+  sampler.stop()
+
+  t = torch.tensor([total_ms, e2e_ms, e2e_wall_ms], dtype=torch.float64, device=device)
+  if world > 1:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    stats = env.episode_statistics(all_gather=True)   # the framework's only collective
+  else:
+    stats = env.episode_statistics()[None]
+  total_ms, e2e_ms, e2e_wall_ms = (float(x) for x in t.cpu())
+  diag = env.client.diag.cpu().numpy()
+
+  if rank == 0:
+    value = world * n * args.steps / (total_ms * 1e-3)
+    e2e_value = world * n * e2e_steps / (max(e2e_ms, e2e_wall_ms) * 1e-3)
+    peak, peak_kind = hbm_peak()
+    launch_ms = float(per_step_ms.mean())
+    achieved = BYTES_PER_ENV_STEP * n / (launch_ms * 1e-3) / 1e9
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'envs_per_gpu': n, 'dt': DT, 'obs_dim': 21,
+                   'program': 'TorsoIMU+MotorEncoder, 1xUprightReward, PerpetualTermination',
+                   'actions': 'U(-2pi,2pi)^12 fresh each step, generated on device outside the timed spans',
+                   'l2': 'flushed between timed steps (256 MiB fill)' if flush is not None else 'not flushed',
+                   'block_threads': env.client.block_size(),
+                   'timing': 'CUDA events around every step on the launching stream, summed; max over ranks'},
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': None, 'peak_source': peak_kind,
+                     'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': 'step_kernel<2,false>',
+                     'launch_ms_mean': launch_ms, 'launch_ms_p50': float(np.median(per_step_ms)),
+                     'launch_ms_max': float(per_step_ms.max()),
+                     'note': 'path is FP32-issue/latency bound, not HBM bound (SURVEY.md 8d)'},
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * n * 12 * 4,
+                'd2h_bytes_per_step': world * n * (21 * 4 + 4 + 1), 'steps': e2e_steps,
+                'api': 'Solo8VanillaEnv.step_host -> solo_step_host (pinned host buffers)',
+                'checksum': checksum},
+        'gpu_launches': int(launches),
+        'clocks': sampler.summary(),
+        'solver': {'mean_contacts_per_env_step': float(diag[0]) / max(1.0, float(diag[3])),
+                   'mean_pgs_iterations': float(diag[1]) / max(1.0, float(diag[3])),
+                   'nan_restores': int(diag[2])},
+        'episode_stats_ranks': int(stats.shape[0]),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+      threads = os.cpu_count() or 1
+      c_envs, c_steps = 1024, 40
+      cv, ct = run_cpu(c_envs, c_steps, 2, threads)
+      line['cpu_baseline'] = {'value': cv, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                              'sample': '%d envs x %d steps of the same workload (%.1f s), oracle port: '
+                                        'C double physics on %d pthreads + numpy epilogue'
+                                        % (c_envs, c_steps, ct, threads)}
+    print(json.dumps(line), flush=True)
+  env.close()
+  if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+  main()

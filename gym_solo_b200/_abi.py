@@ -108,11 +108,11 @@ class SoloProgram(C.Structure):
   ]
 
 
-MODELS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'models')
+MODELS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'assets')
 
 
 def load_model_blob(name_or_path):
-  """Read a compiled model JSON (gym_solo_b200/models/compile_model.py)."""
+  """Read a compiled model JSON (gym_solo_b200/assets/compile_model.py)."""
   path = name_or_path
   if not os.path.exists(path):
     path = os.path.join(MODELS_DIR, name_or_path + '.json')

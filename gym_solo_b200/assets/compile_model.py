@@ -21,7 +21,7 @@ Collision reduction (ours): each hull is reduced to a small support-point set
 leg; 8 rim points of the foot disc) because the ground is the plane z = 0 and a
 convex hull touches a plane at its support point in the -n direction.
 
-usage: python -m gym_solo_b200.models.compile_model <urdf> <out.json> [--name N]
+usage: python -m gym_solo_b200.assets.compile_model <urdf> <out.json> [--name N]
 """
 import json
 import math

@@ -1,0 +1,269 @@
+"""BatchedClient -- what `pybullet_utils.bullet_client.BulletClient` is to the
+reference env, for `num_envs` environments resident on one B200.
+
+It owns the C-ABI handle (include/solo8_b200.h) and the torch tensors the
+handle is bound to, and exposes the subset of the BulletClient surface that
+gym_solo's env and plug-ins call, batched:
+
+  setJointMotorControlArray + stepSimulation   -> simulate(actions)
+  getBasePositionAndOrientation(robot)         -> (pos [N,3], quat [N,4])
+  getEulerFromQuaternion(quat)                 -> [N,3]
+  getBaseVelocity(robot)                       -> (lin [N,3], ang [N,3])
+  getJointState(robot, j)                      -> (q [N], qdot [N], zeros, zeros)
+  getNumJoints(robot) / getJointInfo(robot, j)
+
+so that user-written Observation / Reward subclasses keep working with tensors
+in place of floats.  torch is used for device memory and streams only; all
+arithmetic of the step path happens in the CUDA library.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from gym_solo_b200 import _abi
+from gym_solo_b200 import _lib
+
+ROBOT_ID = 1   # plane is body 0, robot body 1 (solo8_base_env.py:47, solo8v2vanilla.py:151)
+
+_SNAPSHOT_CACHE = {}
+
+
+def _ptr(t):
+  return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _struct_key(s):
+  return bytes(memoryview(s))
+
+
+class BatchedClient:
+  def __init__(self, model_blob, model, config, num_envs, device):
+    self.lib = _lib.load()
+    self.device = torch.device(device)
+    if self.device.type != 'cuda':
+      raise ValueError('gym_solo_b200 runs on CUDA devices only (got %r)' % (device,))
+    if not torch.cuda.is_available():
+      raise _lib.SoloError('no CUDA device: the Solo 8 step path has no CPU fallback')
+    self.index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+    self.device = torch.device('cuda', self.index)
+    self.blob, self.model, self.config = model_blob, model, config
+    self.n = int(num_envs)
+    self.ndof, self.n_api = model.ndof, model.n_api
+    self.sdim = _abi.state_dim(model.ndof)
+    self.api_dof = [model.api_dof[i] for i in range(model.n_api)]
+    self.handle = C.c_void_p()
+    _lib.check(self.lib.solo_create(C.byref(model), C.byref(config), self.n, self.index,
+                                    C.byref(self.handle)))
+    dev = self.device
+    self.state = torch.zeros((self.sdim, self.n), dtype=torch.float32, device=dev)
+    self.counters = torch.zeros((_abi.MAX_TERM_TERMS, self.n), dtype=torch.int32, device=dev)
+    self.snapshot = torch.zeros((self.sdim,), dtype=torch.float32, device=dev)
+    self.stats = torch.zeros((4, self.n), dtype=torch.float32, device=dev)
+    self.diag = torch.zeros((4,), dtype=torch.int64, device=dev)
+    _lib.check(self.lib.solo_bind(self.handle, _ptr(self.state), _ptr(self.counters),
+                                  _ptr(self.snapshot), _ptr(self.stats), None), self.handle)
+    _lib.check(self.lib.solo_bind_diag(self.handle, _ptr(self.diag)), self.handle)
+    self._program_token = None
+    self._dbg = None
+    self._staging = None
+
+  # ---- lifetime ---------------------------------------------------------------
+  def disconnect(self):
+    if self.handle:
+      self.lib.solo_destroy(self.handle)
+      self.handle = C.c_void_p()
+
+  def __del__(self):
+    try:
+      self.disconnect()
+    except Exception:
+      pass
+
+  def _stream(self):
+    return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+  # ---- program ----------------------------------------------------------------
+  def set_program(self, program, token=None):
+    """Install the fused epilogue tables; `token` lets callers skip re-installing
+    the program that is already active."""
+    if token is not None and token == self._program_token:
+      return
+    _lib.check(self.lib.solo_set_program(self.handle, C.byref(program)), self.handle)
+    self._program_token = token
+
+  def obs_dim(self):
+    return self.lib.solo_obs_dim(self.handle)
+
+  # ---- state ------------------------------------------------------------------
+  def initial_state(self, pos, euler):
+    """State right after loadURDF (solo8v2vanilla.py:151-155)."""
+    s = np.zeros(self.sdim, dtype=np.float64)
+    s[0:3] = pos
+    s[3:7] = quaternion_from_euler(euler)
+    return s
+
+  def set_state(self, state):
+    """state: [sdim] (broadcast) or [N, sdim]; numpy or tensor."""
+    t = torch.as_tensor(np.asarray(state) if not torch.is_tensor(state) else state)
+    t = t.to(device=self.device, dtype=torch.float32)
+    if t.dim() == 1:
+      self.state.copy_(t[:, None].expand(self.sdim, self.n))
+    else:
+      self.state.copy_(t.t())
+
+  def get_state(self):
+    """[N, sdim] float32 copy (pos 3, quat 4, lin 3, ang 3, q, qdot)."""
+    return self.state.t().contiguous()
+
+  def set_snapshot(self, state):
+    self.snapshot.copy_(torch.as_tensor(np.asarray(state, dtype=np.float32)).to(self.device))
+
+  def settle_snapshot(self, start_targets_api, pos, euler, n_steps=500):
+    """reset()'s settle (solo8v2vanilla.py:124-136) computed ONCE per (model,
+    config, start pose): a one-environment handle runs the 500
+    POSITION_CONTROL steps on the GPU; every later reset restores the result."""
+    cfg = _abi.SoloConfig.from_buffer_copy(self.config)
+    cfg.control_mode = _abi.CONTROL_POSITION
+    cfg.num_substeps = 1
+    key = (_struct_key(self.model), _struct_key(cfg), tuple(float(x) for x in start_targets_api),
+           tuple(pos), tuple(euler), n_steps, self.index)
+    snap = _SNAPSHOT_CACHE.get(key)
+    if snap is None:
+      one = BatchedClient(self.blob, self.model, cfg, 1, self.device)
+      one.set_state(one.initial_state(pos, euler))
+      a = torch.tensor(np.asarray(start_targets_api, dtype=np.float32), device=self.device)
+      one.simulate(a, n_steps=n_steps, broadcast=True)
+      snap = one.get_state()[0].double().cpu().numpy()
+      one.disconnect()
+      _SNAPSHOT_CACHE[key] = snap
+    self.set_snapshot(snap)
+    return snap
+
+  def reset(self, mask=None):
+    m = None
+    if mask is not None:
+      m = torch.as_tensor(mask).to(device=self.device, dtype=torch.uint8).contiguous()
+    _lib.check(self.lib.solo_reset(self.handle, _ptr(m), self._stream()), self.handle)
+
+  # ---- stepping ---------------------------------------------------------------
+  def _actions(self, actions, broadcast=False):
+    a = actions if torch.is_tensor(actions) else torch.as_tensor(np.asarray(actions, dtype=np.float32))
+    a = a.to(device=self.device, dtype=torch.float32)
+    if broadcast:
+      if a.shape != (self.n_api,):
+        raise ValueError('broadcast action must have shape (%d,)' % self.n_api)
+    else:
+      if a.dim() == 1 and self.n == 1:
+        a = a[None]
+      if a.shape != (self.n, self.n_api):
+        raise ValueError('actions must have shape (%d, %d), got %s' % (self.n, self.n_api, tuple(a.shape)))
+    return a.contiguous()
+
+  def simulate(self, actions, n_steps=1, broadcast=False):
+    """setJointMotorControlArray + stepSimulation, n_steps times."""
+    a = self._actions(actions, broadcast)
+    _lib.check(self.lib.solo_simulate(self.handle, _ptr(a), 1 if broadcast else 0, int(n_steps),
+                                      self._stream()), self.handle)
+
+  def step(self, actions, scale, obs, reward, done, terminal_obs=None):
+    a = self._actions(actions)
+    _lib.check(self.lib.solo_step(self.handle, _ptr(a), float(scale), _ptr(obs), _ptr(reward), _ptr(done),
+                                  _ptr(terminal_obs), self._stream()), self.handle)
+
+  def observe(self, obs):
+    _lib.check(self.lib.solo_observe(self.handle, _ptr(obs), self._stream()), self.handle)
+
+  def reward(self, out):
+    _lib.check(self.lib.solo_reward(self.handle, _ptr(out), self._stream()), self.handle)
+
+  def bind_staging(self, obs_dim):
+    dev = self.device
+    self._staging = (torch.empty((self.n, self.n_api), dtype=torch.float32, device=dev),
+                     torch.empty((self.n, obs_dim), dtype=torch.float32, device=dev),
+                     torch.empty((self.n,), dtype=torch.float32, device=dev),
+                     torch.empty((self.n,), dtype=torch.uint8, device=dev))
+    _lib.check(self.lib.solo_bind_staging(self.handle, *[_ptr(t) for t in self._staging]), self.handle)
+
+  def step_host(self, actions_np, scale, obs_np, reward_np, done_np):
+    """Host buffers in, host buffers out (the reference's calling convention)."""
+    _lib.check(self.lib.solo_step_host(
+        self.handle, C.c_void_p(actions_np.ctypes.data), float(scale), C.c_void_p(obs_np.ctypes.data),
+        C.c_void_p(reward_np.ctypes.data), C.c_void_p(done_np.ctypes.data), self._stream()), self.handle)
+
+  def enable_debug(self, on=True):
+    """Record per-step contact normal forces [n_cand, N] and applied motor
+    torques [ndof, N] (getContactPoints()[9] / getJointState()[3])."""
+    if on:
+      self._dbg = (torch.zeros((self.model.n_cand, self.n), dtype=torch.float32, device=self.device),
+                   torch.zeros((self.ndof, self.n), dtype=torch.float32, device=self.device))
+      _lib.check(self.lib.solo_bind_debug(self.handle, _ptr(self._dbg[0]), _ptr(self._dbg[1])), self.handle)
+    else:
+      self._dbg = None
+      _lib.check(self.lib.solo_bind_debug(self.handle, None, None), self.handle)
+    return self._dbg
+
+  def launch_count(self):
+    return int(self.lib.solo_launch_count(self.handle))
+
+  def block_size(self):
+    return int(self.lib.solo_block_size(self.handle))
+
+  # ---- BulletClient getters, batched -------------------------------------------
+  def getBasePositionAndOrientation(self, body=ROBOT_ID):
+    return self.state[0:3].t(), self.state[3:7].t()
+
+  def getBaseVelocity(self, body=ROBOT_ID):
+    return self.state[7:10].t(), self.state[10:13].t()
+
+  def getEulerFromQuaternion(self, quat):
+    return euler_from_quaternion(quat)
+
+  def getQuaternionFromEuler(self, euler):
+    return tuple(quaternion_from_euler(euler))
+
+  def getNumJoints(self, body=ROBOT_ID):
+    return self.n_api
+
+  def getJointInfo(self, body, j):
+    """Tuple shaped like pybullet's: [1] name (bytes), [2] type (0 revolute,
+    4 fixed), [8]/[9] limits, [12] child link name."""
+    name = self.blob['api_names'][j]
+    fixed = self.api_dof[j] < 0
+    return (j, name.encode('UTF-8'), 4 if fixed else 0, -1 if fixed else 7 + self.api_dof[j],
+            -1 if fixed else 6 + self.api_dof[j], 0, 0.0, 0.0,
+            float(self.model.api_lower[j]), float(self.model.api_upper[j]), 1000.0, 1000.0,
+            name.encode('UTF-8'))
+
+  def getJointState(self, body, j):
+    d = self.api_dof[j]
+    z = torch.zeros((self.n,), dtype=torch.float32, device=self.device)
+    if d < 0:
+      return z, z, (0.,) * 6, z
+    return self.state[_abi.STATE_BASE + d], self.state[_abi.STATE_BASE + self.ndof + d], (0.,) * 6, z
+
+
+def quaternion_from_euler(e):
+  """pybullet.getQuaternionFromEuler (solo8v2vanilla.py:153): (x, y, z, w)."""
+  r, p, y = (0.5 * float(v) for v in e)
+  cr, sr, cp, sp, cy, sy = math.cos(r), math.sin(r), math.cos(p), math.sin(p), math.cos(y), math.sin(y)
+  return np.array([sr * cp * cy - cr * sp * sy, cr * sp * cy + sr * cp * sy,
+                   cr * cp * sy - sr * sp * cy, cr * cp * cy + sr * sp * sy])
+
+
+def euler_from_quaternion(quat):
+  """pybullet.getEulerFromQuaternion on a [N,4] tensor (for user plug-ins; the
+  fused path computes this in the kernel: solo_core.h euler_from_quat)."""
+  q = torch.as_tensor(quat)
+  x, y, z, w = q[..., 0], q[..., 1], q[..., 2], q[..., 3]
+  sarg = -2.0 * (x * z - w * y)
+  roll = torch.atan2(2 * (y * z + w * x), w * w - x * x - y * y + z * z)
+  pitch = torch.asin(torch.clamp(sarg, -1.0, 1.0))
+  yaw = torch.atan2(2 * (x * y + w * z), w * w + x * x - y * y - z * z)
+  hi, lo = sarg >= 0.99999, sarg <= -0.99999
+  zero = torch.zeros_like(roll)
+  roll = torch.where(hi | lo, zero, roll)
+  pitch = torch.where(hi, zero + 0.5 * math.pi, torch.where(lo, zero - 0.5 * math.pi, pitch))
+  yaw = torch.where(hi, 2 * torch.atan2(-x, y), torch.where(lo, 2 * torch.atan2(x, -y), yaw))
+  return torch.stack([roll, pitch, yaw], dim=-1)

@@ -1,0 +1,302 @@
+// solo_abi.cu -- the C-ABI of include/solo8_b200.h over the sm_100a kernels.
+// No torch types, no CPU fallback: without a CUDA device solo_create fails with
+// SOLO_ENOGPU and nothing else can be called.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
+#include "../../include/solo8_b200.h"
+#include "solo_convert.h"
+#include "solo_kernels.cuh"
+
+using namespace solo;
+
+struct SoloHandle_ {
+  KParams K;
+  Buffers B;
+  int device;
+  int ch;                 // kernel instantiation: max chain length (2 or 3)
+  int state_dim;
+  int obs_dim;
+  int block;              // threads per block
+  bool program_set;
+  bool bound;
+  // staging (solo_step_host)
+  float *st_actions, *st_obs, *st_reward;
+  uint8_t *st_done;
+  int64_t launches;
+  std::string err;
+};
+
+static thread_local std::string g_err;
+
+static int fail(SoloHandle h, int code, const std::string &msg) {
+  if (h) h->err = msg;
+  g_err = msg;
+  return code;
+}
+static int cuda_fail(SoloHandle h, cudaError_t e, const char *what) {
+  return fail(h, SOLO_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+struct DeviceGuard {
+  int prev;
+  bool ok;
+  explicit DeviceGuard(int dev) : prev(-1), ok(true) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+static int pick_block(int n_envs) {
+  const char *e = getenv("SOLO_BLOCK");
+  if (e) {
+    int b = atoi(e);
+    if (b == 32 || b == 64 || b == 128) return b;
+  }
+  // 148 SMs: keep every SM busy for small batches, fewer larger blocks once
+  // there are several warps per SM anyway
+  if (n_envs <= 148 * 64) return 32;
+  if (n_envs <= 148 * 512) return 64;
+  return 128;
+}
+
+static size_t tile_smem(const SoloHandle h) {
+  int k = h->K.M.n_api > h->obs_dim ? h->K.M.n_api : h->obs_dim;
+  return (size_t)h->block * (size_t)(k | 1) * sizeof(float);
+}
+
+template <typename F>
+static int opt_in_smem(SoloHandle h, F *kernel, size_t bytes) {
+  if (bytes <= 48 * 1024) return SOLO_OK;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaFuncSetAttribute");
+  return SOLO_OK;
+}
+
+extern "C" {
+
+const char *solo_version(void) { return "solo8_b200 0.1 (sm_100a)"; }
+
+const char *solo_last_error(SoloHandle h) { return h ? h->err.c_str() : g_err.c_str(); }
+
+int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs, int32_t device,
+                SoloHandle *out) {
+  if (!model || !config || !out) return fail(nullptr, SOLO_EINVAL, "null argument");
+  *out = nullptr;
+  if (n_envs < 1) return fail(nullptr, SOLO_EINVAL, "n_envs must be >= 1");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count < 1) {
+    cudaGetLastError();
+    return fail(nullptr, SOLO_ENOGPU, "no CUDA device: the Solo 8 step path has no CPU fallback");
+  }
+  if (device < 0 || device >= count) return fail(nullptr, SOLO_EINVAL, "device index out of range");
+  SoloHandle h = new SoloHandle_();
+  memset(&h->K, 0, sizeof h->K);
+  memset(&h->B, 0, sizeof h->B);
+  std::string msg = convert_model<float>(*model, config->plane_friction, &h->K.M);
+  if (msg.empty()) msg = convert_config<float>(*config, &h->K.C);
+  if (!msg.empty()) { delete h; return fail(nullptr, SOLO_EINVAL, msg); }
+  h->device = device;
+  h->ch = max_chain(*model) <= 2 ? 2 : 3;
+  h->state_dim = SOLO_STATE_DIM(model->ndof);
+  h->obs_dim = 0;
+  h->block = pick_block(n_envs);
+  h->program_set = false;
+  h->bound = false;
+  h->B.n = n_envs;
+  h->st_actions = h->st_obs = h->st_reward = nullptr;
+  h->st_done = nullptr;
+  h->launches = 0;
+  {
+    DeviceGuard g(device);
+    if (!g.ok) { delete h; return fail(nullptr, SOLO_ECUDA, "cudaSetDevice failed"); }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess && prop.major < 10) {
+      delete h;
+      return fail(nullptr, SOLO_ENOGPU, "device is not sm_100 class: this library is built for sm_100a only");
+    }
+  }
+  *out = h;
+  return SOLO_OK;
+}
+
+int solo_destroy(SoloHandle h) {
+  if (!h) return SOLO_EINVAL;
+  delete h;
+  return SOLO_OK;
+}
+
+int solo_set_program(SoloHandle h, const SoloProgram *program) {
+  if (!h || !program) return fail(h, SOLO_EINVAL, "null argument");
+  int dim = 0;
+  std::string msg = check_program(*program, h->K.M.n_api, &dim);
+  if (!msg.empty()) return fail(h, SOLO_EINVAL, msg);
+  memcpy(&h->K.P, program, sizeof h->K.P);
+  h->obs_dim = dim;
+  h->B.obs_dim = dim;
+  h->program_set = true;
+  DeviceGuard g(h->device);
+  const size_t sm = tile_smem(h);
+  int rc = SOLO_OK;
+  if (h->ch == 2) {
+    if (!rc) rc = opt_in_smem(h, step_kernel<2, false>, sm);
+    if (!rc) rc = opt_in_smem(h, step_kernel<2, true>, sm);
+    if (!rc) rc = opt_in_smem(h, observe_kernel<2>, sm);
+  } else {
+    if (!rc) rc = opt_in_smem(h, step_kernel<3, false>, sm);
+    if (!rc) rc = opt_in_smem(h, step_kernel<3, true>, sm);
+    if (!rc) rc = opt_in_smem(h, observe_kernel<3>, sm);
+  }
+  return rc;
+}
+
+int solo_obs_dim(SoloHandle h) { return h ? h->obs_dim : SOLO_EINVAL; }
+
+int64_t solo_scratch_bytes(SoloHandle h) {
+  (void)h;
+  return 0;   // contact rows live in thread-local memory
+}
+
+int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snapshot_dev, float *stats_dev,
+              void *scratch_dev) {
+  (void)scratch_dev;
+  if (!h || !state_dev || !counters_dev || !snapshot_dev) return fail(h, SOLO_EINVAL, "null buffer");
+  h->B.state = state_dev;
+  h->B.counters = counters_dev;
+  h->B.snapshot = snapshot_dev;
+  h->B.stats = stats_dev;
+  h->bound = true;
+  return SOLO_OK;
+}
+
+int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev) {
+  if (!h) return SOLO_EINVAL;
+  h->B.diag = diag_dev;
+  return SOLO_OK;
+}
+
+int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev) {
+  if (!h) return SOLO_EINVAL;
+  h->B.dbg_normal_force = normal_force_dev;
+  h->B.dbg_motor_torque = motor_torque_dev;
+  return SOLO_OK;
+}
+
+int solo_bind_staging(SoloHandle h, float *actions_dev, float *obs_dev, float *reward_dev, uint8_t *done_dev) {
+  if (!h || !actions_dev || !obs_dev || !reward_dev || !done_dev) return fail(h, SOLO_EINVAL, "null buffer");
+  h->st_actions = actions_dev; h->st_obs = obs_dev; h->st_reward = reward_dev; h->st_done = done_dev;
+  return SOLO_OK;
+}
+
+static int check_launch(SoloHandle h, const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(h, e, what);
+  h->launches++;
+  return SOLO_OK;
+}
+
+int solo_simulate(SoloHandle h, const float *actions_dev, int32_t broadcast, int32_t n_steps, void *stream) {
+  if (!h || !actions_dev) return fail(h, SOLO_EINVAL, "null argument");
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  if (n_steps < 0) return fail(h, SOLO_EINVAL, "n_steps must be >= 0");
+  if (n_steps == 0) return SOLO_OK;
+  DeviceGuard g(h->device);
+  const int grid = (h->B.n + h->block - 1) / h->block;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
+  if (h->ch == 2) {
+    if (dbg) simulate_kernel<2, true><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
+    else simulate_kernel<2, false><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
+  } else {
+    if (dbg) simulate_kernel<3, true><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
+    else simulate_kernel<3, false><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
+  }
+  return check_launch(h, "simulate_kernel");
+}
+
+int solo_step(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev, float *reward_dev,
+              uint8_t *done_dev, float *terminal_obs_dev, void *stream) {
+  if (!h || !actions_dev || !obs_dev || !reward_dev || !done_dev) return fail(h, SOLO_EINVAL, "null argument");
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  if (!h->program_set || h->obs_dim < 1) return fail(h, SOLO_EINVAL, "no observation program set");
+  DeviceGuard g(h->device);
+  const int grid = (h->B.n + h->block - 1) / h->block;
+  const size_t sm = tile_smem(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
+#define SOLO_LAUNCH_STEP(CHV, DBGV)                                                              \
+  step_kernel<CHV, DBGV><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, action_scale, obs_dev, \
+                                                     reward_dev, done_dev, terminal_obs_dev)
+  if (h->ch == 2) { if (dbg) SOLO_LAUNCH_STEP(2, true); else SOLO_LAUNCH_STEP(2, false); }
+  else { if (dbg) SOLO_LAUNCH_STEP(3, true); else SOLO_LAUNCH_STEP(3, false); }
+#undef SOLO_LAUNCH_STEP
+  return check_launch(h, "step_kernel");
+}
+
+static int observe_impl(SoloHandle h, float *obs_dev, float *reward_dev, void *stream) {
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  if (!h->program_set) return fail(h, SOLO_EINVAL, "no program set");
+  if (obs_dev && h->obs_dim < 1) return fail(h, SOLO_EINVAL, "no observation program set");
+  DeviceGuard g(h->device);
+  const int grid = (h->B.n + h->block - 1) / h->block;
+  const size_t sm = tile_smem(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->ch == 2) observe_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, obs_dev, reward_dev);
+  else observe_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, obs_dev, reward_dev);
+  return check_launch(h, "observe_kernel");
+}
+
+int solo_observe(SoloHandle h, float *obs_dev, void *stream) {
+  if (!h || !obs_dev) return fail(h, SOLO_EINVAL, "null argument");
+  return observe_impl(h, obs_dev, nullptr, stream);
+}
+
+int solo_reward(SoloHandle h, float *reward_dev, void *stream) {
+  if (!h || !reward_dev) return fail(h, SOLO_EINVAL, "null argument");
+  if (h->program_set && h->K.P.n_rew < 1) return fail(h, SOLO_EINVAL, "no reward program set");
+  return observe_impl(h, nullptr, reward_dev, stream);
+}
+
+int solo_reset(SoloHandle h, const uint8_t *mask_dev, void *stream) {
+  if (!h) return SOLO_EINVAL;
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  DeviceGuard g(h->device);
+  const int block = 128;
+  const int grid = (h->B.n + block - 1) / block;
+  reset_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(h->B, h->state_dim, mask_dev);
+  return check_launch(h, "reset_kernel");
+}
+
+int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, float *obs_host,
+                   float *reward_host, uint8_t *done_host, void *stream) {
+  if (!h || !actions_host || !obs_host || !reward_host || !done_host) return fail(h, SOLO_EINVAL, "null argument");
+  if (!h->st_actions) return fail(h, SOLO_EINVAL, "solo_bind_staging has not been called");
+  DeviceGuard g(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t n = (size_t)h->B.n;
+  cudaError_t e = cudaMemcpyAsync(h->st_actions, actions_host, n * h->K.M.n_api * sizeof(float),
+                                  cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return cuda_fail(h, e, "H2D actions");
+  int rc = solo_step(h, h->st_actions, action_scale, h->st_obs, h->st_reward, h->st_done, nullptr, stream);
+  if (rc) return rc;
+  e = cudaMemcpyAsync(obs_host, h->st_obs, n * h->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, h->st_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(done_host, h->st_done, n, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return cuda_fail(h, e, "D2H results");
+  return SOLO_OK;
+}
+
+int64_t solo_launch_count(SoloHandle h) { return h ? h->launches : 0; }
+
+int solo_block_size(SoloHandle h) { return h ? h->block : SOLO_EINVAL; }
+
+}  // extern "C"

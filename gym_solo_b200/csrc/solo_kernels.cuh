@@ -1,0 +1,285 @@
+// solo_kernels.cuh -- sm_100a kernels of the Solo 8 env-step path.
+//
+// One thread per environment.  The per-environment arithmetic is
+// solo_core.h (float32); this file adds the batched memory plan:
+//   * constant tables (model, config, epilogue program) travel as ONE
+//     __grid_constant__ kernel parameter, i.e. they sit in the constant bank
+//     and every warp-uniform read is an LDC / direct FFMA operand -- no staging
+//     loop, no shared-memory bank traffic, and no module-global state, so two
+//     handles with different robots can coexist in one process;
+//   * state is structure-of-arrays state[field][env]: every load/store of a
+//     field is one fully coalesced 128 B line per warp, exactly once per
+//     env.step (read at entry, written at exit; substeps stay in registers);
+//   * actions arrive and observations leave in the reference's [env][k] layout
+//     (solo8v2vanilla.py:72-102) and are transposed through shared memory so
+//     that the global side is again whole lines;
+//   * the contact rows of the PGS sweep live in thread-local memory, which the
+//     hardware interleaves per lane (row i of 32 envs = 32 consecutive words).
+#ifndef SOLO_KERNELS_CUH_
+#define SOLO_KERNELS_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "solo_core.h"
+
+namespace solo {
+
+struct KParams {
+  ModelT<float> M;
+  ConfigT<float> C;
+  ProgramC P;
+};
+static_assert(sizeof(KParams) < 16384, "constant tables must fit the kernel parameter bank");
+
+struct Buffers {
+  float *state;              // [state_dim][n]
+  int32_t *counters;         // [kMaxTermTerms][n]
+  const float *snapshot;     // [state_dim]
+  float *stats;              // [4][n] or null: running return, running length, last return, episodes
+  unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, env-steps
+  float *dbg_normal_force;   // [n_cand][n] or null
+  float *dbg_motor_torque;   // [ndof][n] or null
+  int32_t n;
+  int32_t obs_dim;
+};
+
+__device__ __forceinline__ bool state_finite(const float *p, int n) {
+  float acc = 0.f;
+  for (int i = 0; i < n; i++) acc += p[i] * 0.f;   // NaN/Inf propagate, finite -> 0
+  return acc == 0.f;
+}
+
+template <int CH>
+__device__ __forceinline__ bool env_finite(const EnvState<float, CH> &s) {
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; i++) acc += (s.pos[i] + s.vlin[i] + s.vang[i]) * 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; i++) acc += s.quat[i] * 0.f;
+#pragma unroll
+  for (int l = 0; l < kLegs; l++)
+#pragma unroll
+    for (int j = 0; j < CH; j++) acc += (s.q[l][j] + s.qd[l][j]) * 0.f;
+  return acc == 0.f;
+}
+
+template <int CH>
+__device__ __forceinline__ void load_snapshot(const ModelT<float> &M, const float *snap, EnvState<float, CH> &s) {
+  load_state<float, CH, float>(M, snap, 1, s);
+}
+
+__device__ __forceinline__ void diag_add(unsigned long long *diag, int contacts, int iters, int nan, int steps) {
+  // warp-level reduction, one atomic per warp and counter
+  const unsigned mask = __activemask();
+  for (int off = 16; off > 0; off >>= 1) {
+    contacts += __shfl_down_sync(mask, contacts, off);
+    iters += __shfl_down_sync(mask, iters, off);
+    nan += __shfl_down_sync(mask, nan, off);
+    steps += __shfl_down_sync(mask, steps, off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(diag + 0, (unsigned long long)contacts);
+    atomicAdd(diag + 1, (unsigned long long)iters);
+    if (nan) atomicAdd(diag + 2, (unsigned long long)nan);
+    atomicAdd(diag + 3, (unsigned long long)steps);
+  }
+}
+
+// Block-cooperative transpose of a [rows = blockDim.x envs][k] tile between the
+// reference's row-major layout in global memory and one value per thread.
+//   gather : tile[t][j] (global, row-major, contiguous) -> smem, then thread t reads its row
+//   scatter: thread t writes its row to smem, then the tile is stored contiguous
+// smem holds blockDim.x * k floats; rows are padded to an odd stride to keep the
+// per-thread row accesses conflict free.
+__device__ __forceinline__ int pad_stride(int k) { return k | 1; }
+
+__device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t env0, int n_valid, int k,
+                                            float *sm) {
+  const int ps = pad_stride(k);
+  const int total = n_valid * k;
+  const float *src = g + env0 * k;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int r = i / k, c = i - r * k;
+    sm[r * ps + c] = src[i];
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0, int n_valid, int k,
+                                             const float *sm) {
+  const int ps = pad_stride(k);
+  const int total = n_valid * k;
+  float *dst = g + env0 * k;
+  __syncthreads();
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int r = i / k, c = i - r * k;
+    dst[i] = sm[r * ps + c];
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// env.step for every env (solo8v2vanilla.py:72-102)
+// ---------------------------------------------------------------------------------
+template <int CH, bool DBG>
+__global__ void __launch_bounds__(128)
+step_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__restrict__ actions,
+            const float action_scale, float *__restrict__ obs_out, float *__restrict__ reward_out,
+            uint8_t *__restrict__ done_out, float *__restrict__ terminal_obs_out) {
+  extern __shared__ float smem[];
+  const ModelT<float> &M = K.M;
+  const ConfigT<float> &C = K.C;
+  const ProgramC &P = K.P;
+  const int64_t env0 = (int64_t)blockIdx.x * blockDim.x;
+  const int64_t env = env0 + threadIdx.x;
+  const int n_valid = (int)min((int64_t)blockDim.x, (int64_t)B.n - env0);
+  const bool live = env < B.n;
+  const int n_api = M.n_api;
+
+  // actions: [env][n_api] -> per-thread command
+  tile_gather(actions, env0, n_valid, n_api, smem);
+  float cmd[kLegs][CH];
+  if (live) load_command<float, CH, float>(M, smem + threadIdx.x * pad_stride(n_api), action_scale, cmd);
+  __syncthreads();   // smem is reused for the observation tile below
+
+  EnvState<float, CH> s;
+  float ob[kMaxObsDim];
+  float rew = 0.f;
+  bool done = false;
+  int contacts = 0, iters = 0, nan = 0;
+  if (live) {
+    load_state<float, CH, float>(M, B.state + env, B.n, s);
+    float scratch[kMaxContacts * RowLayout<CH>::kContact];
+    DebugOut<float> dbg;
+    dbg.normal_force = DBG && B.dbg_normal_force ? B.dbg_normal_force + env : nullptr;
+    dbg.motor_torque = DBG && B.dbg_motor_torque ? B.dbg_motor_torque + env : nullptr;
+    dbg.stride = B.n;
+    for (int k = 0; k < C.substeps; k++) {
+      StepDiag d;
+      physics_step<float, CH>(M, C, s, cmd, scratch, &d, DBG ? &dbg : nullptr);
+      contacts += d.n_contacts; iters += d.iterations;
+    }
+    if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
+
+    float e[3];
+    euler_from_quat(s.quat, e);
+    compute_obs<float, CH>(M, P, s, e, ob);
+    rew = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
+    done = eval_terminations(P, B.counters + env, B.n);
+
+    if (B.stats) {
+      float ret = B.stats[env] + rew;
+      float len = B.stats[(int64_t)B.n + env] + 1.f;
+      if (done) {
+        B.stats[2 * (int64_t)B.n + env] = ret;
+        B.stats[3 * (int64_t)B.n + env] += 1.f;
+        if (P.auto_reset) { ret = 0.f; len = 0.f; }
+      }
+      B.stats[env] = ret;
+      B.stats[(int64_t)B.n + env] = len;
+    }
+  }
+
+  const int od = B.obs_dim;
+  const int ps = pad_stride(od);
+  if (P.auto_reset) {
+    // terminal observation first (gym.vector convention), then the first
+    // observation of the new episode from the snapshot
+    if (terminal_obs_out) {
+      if (live)
+        for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
+      tile_scatter(terminal_obs_out, env0, n_valid, od, smem);
+      __syncthreads();
+    }
+    if (live && done) {
+      load_snapshot<CH>(M, B.snapshot, s);
+      for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
+      float e[3];
+      euler_from_quat(s.quat, e);
+      compute_obs<float, CH>(M, P, s, e, ob);
+    }
+  }
+  if (live) {
+    store_state<float, CH, float>(M, s, B.state + env, B.n);
+    reward_out[env] = rew;
+    done_out[env] = done ? 1 : 0;
+    for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
+  }
+  tile_scatter(obs_out, env0, n_valid, od, smem);
+  if (B.diag) diag_add(B.diag, contacts, iters, nan, live ? 1 : 0);
+}
+
+// ---------------------------------------------------------------------------------
+// setJointMotorControlArray + stepSimulation, n_steps times with one command
+// (solo8v2vanilla.py:87-91; the 500 settle steps of reset :130-136).  State stays
+// in registers across the steps.
+// ---------------------------------------------------------------------------------
+template <int CH, bool DBG>
+__global__ void __launch_bounds__(128)
+simulate_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__restrict__ actions,
+                const int broadcast, const int n_steps) {
+  const ModelT<float> &M = K.M;
+  const ConfigT<float> &C = K.C;
+  const int64_t env = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  float cmd[kLegs][CH];
+  load_command<float, CH, float>(M, actions + (broadcast ? 0 : env * M.n_api), 1.f, cmd);
+  EnvState<float, CH> s;
+  load_state<float, CH, float>(M, B.state + env, B.n, s);
+  float scratch[kMaxContacts * RowLayout<CH>::kContact];
+  DebugOut<float> dbg;
+  dbg.normal_force = DBG && B.dbg_normal_force ? B.dbg_normal_force + env : nullptr;
+  dbg.motor_torque = DBG && B.dbg_motor_torque ? B.dbg_motor_torque + env : nullptr;
+  dbg.stride = B.n;
+  int contacts = 0, iters = 0, nan = 0;
+  for (int k = 0; k < n_steps; k++) {
+    StepDiag d;
+    physics_step<float, CH>(M, C, s, cmd, scratch, &d, DBG ? &dbg : nullptr);
+    contacts += d.n_contacts; iters += d.iterations;
+  }
+  if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
+  store_state<float, CH, float>(M, s, B.state + env, B.n);
+  if (B.diag) diag_add(B.diag, contacts, iters, nan, n_steps);
+}
+
+// obs_factory.get_obs() / reward_factory.get_reward() on the current state
+// (solo8v2vanilla.py:141-143; rewards.py:104-118)
+template <int CH>
+__global__ void __launch_bounds__(128)
+observe_kernel(const __grid_constant__ KParams K, const Buffers B, float *__restrict__ obs_out,
+               float *__restrict__ reward_out) {
+  extern __shared__ float smem[];
+  const ModelT<float> &M = K.M;
+  const ProgramC &P = K.P;
+  const int64_t env0 = (int64_t)blockIdx.x * blockDim.x;
+  const int64_t env = env0 + threadIdx.x;
+  const int n_valid = (int)min((int64_t)blockDim.x, (int64_t)B.n - env0);
+  const bool live = env < B.n;
+  const int od = B.obs_dim, ps = pad_stride(od);
+  if (live) {
+    EnvState<float, CH> s;
+    load_state<float, CH, float>(M, B.state + env, B.n, s);
+    float e[3];
+    euler_from_quat(s.quat, e);
+    if (obs_out) {
+      float ob[kMaxObsDim];
+      compute_obs<float, CH>(M, P, s, e, ob);
+      for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
+    }
+    if (reward_out) reward_out[env] = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
+  }
+  if (obs_out) tile_scatter(obs_out, env0, n_valid, od, smem);
+}
+
+// env.reset by snapshot restore + termination_factory.reset()
+// (solo8v2vanilla.py:104-143)
+__global__ void reset_kernel(const Buffers B, const int state_dim, const uint8_t *__restrict__ mask) {
+  const int64_t env = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  if (mask && !mask[env]) return;
+  for (int f = 0; f < state_dim; f++) B.state[(int64_t)f * B.n + env] = B.snapshot[f];
+  for (int t = 0; t < kMaxTermTerms; t++) B.counters[(int64_t)t * B.n + env] = 0;
+  if (B.stats) { B.stats[env] = 0.f; B.stats[(int64_t)B.n + env] = 0.f; }
+}
+
+}  // namespace solo
+#endif  // SOLO_KERNELS_CUH_

@@ -41,7 +41,7 @@ extern "C" {
 #define SOLO_ECUDA (-2)
 #define SOLO_ENOGPU (-3)
 
-/* Compiled robot model (written by gym_solo_b200/models/compile_model.py from
+/* Compiled robot model (written by gym_solo_b200/assets/compile_model.py from
  * gym_solo/assets/solo8v2/solo.urdf:8-583).  Body 0 is the floating base in
  * its inertial frame; body 1+d is the child of dof d.  Dofs are chain
  * contiguous: leg l owns dofs [sum(chain_len[:l]), +chain_len[l]). */
@@ -208,6 +208,13 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  * (sum over envs of contact points, PGS iterations run, NaN resets), written to
  * a caller device buffer int64[4] when bound (NULL to disable). */
 int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
+/* Parity harness: per-step contact normal force per support point
+ * (float[n_cand][n_envs], == getContactPoints()[9]) and applied motor torque per
+ * dof (float[ndof][n_envs], == getJointState()[3]) of the last physics step.
+ * NULL disables; binding either selects the instrumented kernel variant. */
+int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev);
+/* Threads per block the handle launches with (one thread per environment). */
+int solo_block_size(SoloHandle h);
 /* How many kernels this handle has launched so far (bench `gpu_launches`). */
 int64_t solo_launch_count(SoloHandle h);
 const char *solo_last_error(SoloHandle h);
