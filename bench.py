@@ -287,11 +287,11 @@ def main():
                    'program': 'TorsoIMU+MotorEncoder, 1xUprightReward, PerpetualTermination',
                    'actions': 'U(-2pi,2pi)^12 fresh each step, generated on device outside the timed spans',
                    'l2': 'flushed between timed steps (256 MiB fill)' if flush is not None else 'not flushed',
-                   'block_threads': env.client.block_size(),
+                   'block_threads': env.client.block_size(), 'solver_envs_per_warp': env.client.solver_lanes(),
                    'timing': 'CUDA events around every step on the launching stream, summed; max over ranks'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': None, 'peak_source': peak_kind,
-                     'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': 'step_kernel<2,false>',
+                     'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': 'setup_kernel<2> + solve_kernel<2,false> + finish_kernel<2> (one env.step)',
                      'launch_ms_mean': launch_ms, 'launch_ms_p50': float(np.median(per_step_ms)),
                      'launch_ms_max': float(per_step_ms.max()),
                      'note': 'path is FP32-issue/latency bound, not HBM bound (SURVEY.md 8d)'},

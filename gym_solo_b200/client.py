@@ -62,8 +62,13 @@ class BatchedClient:
     self.snapshot = torch.zeros((self.sdim,), dtype=torch.float32, device=dev)
     self.stats = torch.zeros((4, self.n), dtype=torch.float32, device=dev)
     self.diag = torch.zeros((4,), dtype=torch.int64, device=dev)
+    # solver scratch: constraint rows, mass-matrix factors, yh, contact headers
+    nbytes = int(self.lib.solo_scratch_bytes(self.handle))
+    if nbytes < 0:
+      raise _lib.SoloError('solo_scratch_bytes failed')
+    self.scratch = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=dev)
     _lib.check(self.lib.solo_bind(self.handle, _ptr(self.state), _ptr(self.counters),
-                                  _ptr(self.snapshot), _ptr(self.stats), None), self.handle)
+                                  _ptr(self.snapshot), _ptr(self.stats), _ptr(self.scratch)), self.handle)
     _lib.check(self.lib.solo_bind_diag(self.handle, _ptr(self.diag)), self.handle)
     self._program_token = None
     self._dbg = None
@@ -209,6 +214,20 @@ class BatchedClient:
 
   def block_size(self):
     return int(self.lib.solo_block_size(self.handle))
+
+  def phase_timing(self, on=True):
+    _lib.check(self.lib.solo_phase_timing(self.handle, 1 if on else 0), self.handle)
+
+  def phase_times(self):
+    """(physics steps timed, [setup_ms, solve_ms, finish_ms] summed) since phase_timing(True)."""
+    ms = (C.c_double * 3)()
+    n = int(self.lib.solo_phase_times(self.handle, ms))
+    if n < 0:
+      raise _lib.SoloError('solo_phase_times failed')
+    return n, [float(ms[0]), float(ms[1]), float(ms[2])]
+
+  def solver_lanes(self):
+    return int(self.lib.solo_solver_lanes(self.handle))
 
   # ---- BulletClient getters, batched -------------------------------------------
   def getBasePositionAndOrientation(self, body=ROBOT_ID):

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/solo8_b200.h"
 #include "solo_convert.h"
@@ -20,13 +21,21 @@ struct SoloHandle_ {
   int ch;                 // kernel instantiation: max chain length (2 or 3)
   int state_dim;
   int obs_dim;
-  int block;              // threads per block
+  int block;              // threads per block of the one-thread-per-env kernels
+  int lanes;              // environments per warp in the solver kernel
+  uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
   bool bound;
   // staging (solo_step_host)
   float *st_actions, *st_obs, *st_reward;
   uint8_t *st_done;
   int64_t launches;
+  // optional live per-phase timing (bench.py roofline): 4 events per physics step
+  bool timing;
+  std::vector<cudaEvent_t> ev;
+  size_t ev_used;
+  double phase_ms[3];
+  int64_t phase_steps;
   std::string err;
 };
 
@@ -65,6 +74,41 @@ static int pick_block(int n_envs) {
   if (n_envs <= 148 * 64) return 32;
   if (n_envs <= 148 * 512) return 64;
   return 128;
+}
+
+// Solver kernel: environments per warp.  A small batch is spread thin so that
+// every SM sub-partition (148 x 4) gets a warp and a warp waits only for the
+// slowest of `lanes` serial chains; large batches fill the warps.
+static int pick_lanes(int n_envs) {
+  const char *e = getenv("SOLO_LANES");
+  if (e) {
+    int l = atoi(e);
+    if (l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32) return l;
+  }
+  int l = 32;
+  while (l > 8 && (n_envs + l - 1) / l < 148 * 4) l >>= 1;
+  return l;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct ScratchLayout {
+  size_t cand, hdr, yh, fac, rows, total;
+};
+static ScratchLayout scratch_layout(const SoloHandle h) {
+  const size_t n = (size_t)h->B.n;
+  const size_t row = h->ch == 2 ? RowLayout<2>::kRow : RowLayout<3>::kRow;
+  const size_t slots = h->ch == 2 ? RowLayout<2>::kSlots : RowLayout<3>::kSlots;
+  const size_t facs = h->ch == 2 ? FactorLayout<2>::kSize : FactorLayout<3>::kSize;
+  ScratchLayout L;
+  size_t off = 0;
+  L.cand = off; off = align256(off + sizeof(float) * 4 * kMaxCand);
+  L.hdr = off;  off = align256(off + sizeof(uint32_t) * 2 * n);
+  L.yh = off;   off = align256(off + sizeof(float) * (6 + kLegs * h->ch) * n);
+  L.fac = off;  off = align256(off + sizeof(float) * facs * n);
+  L.rows = off; off = align256(off + sizeof(float) * slots * n * row);
+  L.total = off;
+  return L;
 }
 
 static size_t tile_smem(const SoloHandle h) {
@@ -109,12 +153,21 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->state_dim = SOLO_STATE_DIM(model->ndof);
   h->obs_dim = 0;
   h->block = pick_block(n_envs);
+  h->lanes = pick_lanes(n_envs);
+  h->motor_mask = 0;
+  if (config->control_mode == SOLO_CONTROL_POSITION)
+    for (int l = 0; l < model->n_legs; l++)
+      for (int i = 0; i < model->chain_len[l]; i++) h->motor_mask |= 1u << (l * h->ch + i);
   h->program_set = false;
   h->bound = false;
   h->B.n = n_envs;
   h->st_actions = h->st_obs = h->st_reward = nullptr;
   h->st_done = nullptr;
   h->launches = 0;
+  h->timing = false;
+  h->ev_used = 0;
+  h->phase_ms[0] = h->phase_ms[1] = h->phase_ms[2] = 0;
+  h->phase_steps = 0;
   {
     DeviceGuard g(device);
     if (!g.ok) { delete h; return fail(nullptr, SOLO_ECUDA, "cudaSetDevice failed"); }
@@ -130,6 +183,7 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
 
 int solo_destroy(SoloHandle h) {
   if (!h) return SOLO_EINVAL;
+  for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
   delete h;
   return SOLO_OK;
 }
@@ -147,12 +201,12 @@ int solo_set_program(SoloHandle h, const SoloProgram *program) {
   const size_t sm = tile_smem(h);
   int rc = SOLO_OK;
   if (h->ch == 2) {
-    if (!rc) rc = opt_in_smem(h, step_kernel<2, false>, sm);
-    if (!rc) rc = opt_in_smem(h, step_kernel<2, true>, sm);
+    if (!rc) rc = opt_in_smem(h, setup_kernel<2>, sm);
+    if (!rc) rc = opt_in_smem(h, finish_kernel<2>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<2>, sm);
   } else {
-    if (!rc) rc = opt_in_smem(h, step_kernel<3, false>, sm);
-    if (!rc) rc = opt_in_smem(h, step_kernel<3, true>, sm);
+    if (!rc) rc = opt_in_smem(h, setup_kernel<3>, sm);
+    if (!rc) rc = opt_in_smem(h, finish_kernel<3>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<3>, sm);
   }
   return rc;
@@ -161,14 +215,32 @@ int solo_set_program(SoloHandle h, const SoloProgram *program) {
 int solo_obs_dim(SoloHandle h) { return h ? h->obs_dim : SOLO_EINVAL; }
 
 int64_t solo_scratch_bytes(SoloHandle h) {
-  (void)h;
-  return 0;   // contact rows live in thread-local memory
+  if (!h) return SOLO_EINVAL;
+  return (int64_t)scratch_layout(h).total;   // rows, factors, yh, headers, support-point table
 }
 
 int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snapshot_dev, float *stats_dev,
               void *scratch_dev) {
-  (void)scratch_dev;
-  if (!h || !state_dev || !counters_dev || !snapshot_dev) return fail(h, SOLO_EINVAL, "null buffer");
+  if (!h || !state_dev || !counters_dev || !snapshot_dev || !scratch_dev) return fail(h, SOLO_EINVAL, "null buffer");
+  if (((uintptr_t)scratch_dev & 255) != 0) return fail(h, SOLO_EINVAL, "scratch must be 256-byte aligned");
+  {
+    const ScratchLayout L = scratch_layout(h);
+    char *base = (char *)scratch_dev;
+    h->B.cand_tab = (const float *)(base + L.cand);
+    h->B.hdr = (uint32_t *)(base + L.hdr);
+    h->B.yh = (float *)(base + L.yh);
+    h->B.fac = (float *)(base + L.fac);
+    h->B.rows = (float *)(base + L.rows);
+    float tab[4 * kMaxCand];
+    memset(tab, 0, sizeof tab);
+    for (int c = 0; c < h->K.M.n_cand; c++) {
+      for (int k = 0; k < 3; k++) tab[4 * c + k] = h->K.M.cand_pos[c][k];
+      tab[4 * c + 3] = h->K.M.cand_mu[c];
+    }
+    DeviceGuard g(h->device);
+    cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof tab, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return cuda_fail(h, e, "upload of the support-point table");
+  }
   h->B.state = state_dev;
   h->B.counters = counters_dev;
   h->B.snapshot = snapshot_dev;
@@ -203,23 +275,79 @@ static int check_launch(SoloHandle h, const char *what) {
   return SOLO_OK;
 }
 
+// Fold the recorded phase events into the running sums (synchronises on them).
+static int drain_phase_events(SoloHandle h) {
+  for (size_t i = 0; i + 4 <= h->ev_used; i += 4) {
+    cudaError_t e = cudaEventSynchronize(h->ev[i + 3]);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaEventSynchronize");
+    for (int p = 0; p < 3; p++) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, h->ev[i + p], h->ev[i + p + 1]);
+      h->phase_ms[p] += ms;
+    }
+    h->phase_steps++;
+  }
+  h->ev_used = 0;
+  return SOLO_OK;
+}
+
+// One physics step = setup -> solve -> finish on `st`.  epilogue != 0 makes the
+// finish kernel also run observations / reward / termination.
+static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast, float action_scale, int epilogue,
+                          float *obs_dev, float *reward_dev, uint8_t *done_dev, float *terminal_obs_dev,
+                          cudaStream_t st) {
+  const int grid = (h->B.n + h->block - 1) / h->block;
+  const size_t sm = tile_smem(h);
+  const int sgrid = (h->B.n + h->lanes - 1) / h->lanes;
+  const size_t lam_sm = sizeof(float) * 3 * kMaxContacts * h->lanes;
+  const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
+  const int ndof = h->K.M.ndof, n_cand = h->K.M.n_cand;
+  int rc;
+  cudaEvent_t *ev = nullptr;
+  if (h->timing) {
+    if (h->ev_used + 4 > h->ev.size()) {
+      if ((rc = drain_phase_events(h))) return rc;
+    }
+    ev = h->ev.data() + h->ev_used;
+    h->ev_used += 4;
+    cudaEventRecord(ev[0], st);
+  }
+#define SOLO_MARK(i) do { if (ev) cudaEventRecord(ev[i], st); } while (0)
+  if (h->ch == 2) {
+    setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+    if ((rc = check_launch(h, "setup_kernel"))) return rc;
+    SOLO_MARK(1);
+    if (dbg) solve_kernel<2, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    else solve_kernel<2, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    if ((rc = check_launch(h, "solve_kernel"))) return rc;
+    SOLO_MARK(2);
+    finish_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
+  } else {
+    setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+    if ((rc = check_launch(h, "setup_kernel"))) return rc;
+    SOLO_MARK(1);
+    if (dbg) solve_kernel<3, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    else solve_kernel<3, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    if ((rc = check_launch(h, "solve_kernel"))) return rc;
+    SOLO_MARK(2);
+    finish_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
+  }
+  SOLO_MARK(3);
+#undef SOLO_MARK
+  return check_launch(h, "finish_kernel");
+}
+
 int solo_simulate(SoloHandle h, const float *actions_dev, int32_t broadcast, int32_t n_steps, void *stream) {
   if (!h || !actions_dev) return fail(h, SOLO_EINVAL, "null argument");
   if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
   if (n_steps < 0) return fail(h, SOLO_EINVAL, "n_steps must be >= 0");
-  if (n_steps == 0) return SOLO_OK;
   DeviceGuard g(h->device);
-  const int grid = (h->B.n + h->block - 1) / h->block;
-  cudaStream_t st = (cudaStream_t)stream;
-  const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
-  if (h->ch == 2) {
-    if (dbg) simulate_kernel<2, true><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
-    else simulate_kernel<2, false><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
-  } else {
-    if (dbg) simulate_kernel<3, true><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
-    else simulate_kernel<3, false><<<grid, h->block, 0, st>>>(h->K, h->B, actions_dev, broadcast, n_steps);
+  for (int k = 0; k < n_steps; k++) {
+    int rc = launch_physics(h, actions_dev, broadcast, 1.f, 0, nullptr, nullptr, nullptr, nullptr,
+                            (cudaStream_t)stream);
+    if (rc) return rc;
   }
-  return check_launch(h, "simulate_kernel");
+  return SOLO_OK;
 }
 
 int solo_step(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev, float *reward_dev,
@@ -228,17 +356,14 @@ int solo_step(SoloHandle h, const float *actions_dev, float action_scale, float 
   if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
   if (!h->program_set || h->obs_dim < 1) return fail(h, SOLO_EINVAL, "no observation program set");
   DeviceGuard g(h->device);
-  const int grid = (h->B.n + h->block - 1) / h->block;
-  const size_t sm = tile_smem(h);
-  cudaStream_t st = (cudaStream_t)stream;
-  const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
-#define SOLO_LAUNCH_STEP(CHV, DBGV)                                                              \
-  step_kernel<CHV, DBGV><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, action_scale, obs_dev, \
-                                                     reward_dev, done_dev, terminal_obs_dev)
-  if (h->ch == 2) { if (dbg) SOLO_LAUNCH_STEP(2, true); else SOLO_LAUNCH_STEP(2, false); }
-  else { if (dbg) SOLO_LAUNCH_STEP(3, true); else SOLO_LAUNCH_STEP(3, false); }
-#undef SOLO_LAUNCH_STEP
-  return check_launch(h, "step_kernel");
+  const int sub = h->K.C.substeps;
+  for (int k = 0; k < sub; k++) {
+    const int last = k == sub - 1;
+    int rc = launch_physics(h, actions_dev, 0, action_scale, last, obs_dev, reward_dev, done_dev, terminal_obs_dev,
+                            (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return SOLO_OK;
 }
 
 static int observe_impl(SoloHandle h, float *obs_dev, float *reward_dev, void *stream) {
@@ -297,6 +422,31 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, 
 
 int64_t solo_launch_count(SoloHandle h) { return h ? h->launches : 0; }
 
+int solo_phase_timing(SoloHandle h, int32_t enable) {
+  if (!h) return SOLO_EINVAL;
+  DeviceGuard g(h->device);
+  if (enable && h->ev.empty()) {
+    h->ev.resize(4 * 1024);
+    for (auto &e : h->ev)
+      if (cudaEventCreate(&e) != cudaSuccess) return fail(h, SOLO_ECUDA, "cudaEventCreate failed");
+  }
+  h->timing = enable != 0;
+  h->ev_used = 0;
+  h->phase_ms[0] = h->phase_ms[1] = h->phase_ms[2] = 0;
+  h->phase_steps = 0;
+  return SOLO_OK;
+}
+
+int64_t solo_phase_times(SoloHandle h, double *ms3) {
+  if (!h || !ms3) return SOLO_EINVAL;
+  DeviceGuard g(h->device);
+  if (drain_phase_events(h)) return SOLO_ECUDA;
+  for (int p = 0; p < 3; p++) ms3[p] = h->phase_ms[p];
+  return h->phase_steps;
+}
+
 int solo_block_size(SoloHandle h) { return h ? h->block : SOLO_EINVAL; }
+
+int solo_solver_lanes(SoloHandle h) { return h ? h->lanes : SOLO_EINVAL; }
 
 }  // extern "C"

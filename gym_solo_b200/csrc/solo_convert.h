@@ -9,7 +9,7 @@
 #include <string>
 
 #include "../../include/solo8_b200.h"
-#include "solo_core.h"
+#include "solo_phases.h"
 
 namespace solo {
 

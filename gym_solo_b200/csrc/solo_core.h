@@ -108,6 +108,14 @@ enum { kTermPerpetual = 1, kTermTime = 2 };
 // ---- scalar helpers -----------------------------------------------------------
 SOLO_HD float m_sqrt(float x) { return sqrtf(x); }
 SOLO_HD double m_sqrt(double x) { return sqrt(x); }
+SOLO_HD float m_rsqrt(float x) {
+#ifdef __CUDA_ARCH__
+  return rsqrtf(x);
+#else
+  return 1.0f / sqrtf(x);
+#endif
+}
+SOLO_HD double m_rsqrt(double x) { return 1.0 / sqrt(x); }
 SOLO_HD float m_abs(float x) { return fabsf(x); }
 SOLO_HD double m_abs(double x) { return fabs(x); }
 SOLO_HD float m_atan2(float y, float x) { return atan2f(y, x); }
@@ -209,16 +217,6 @@ struct EnvState {
   T q[kLegs][CH], qd[kLegs][CH];
 };
 
-// Row of the whitened constraint system stored in per-thread scratch.
-//   [0..5] Jh base, [6..6+CH) Jh leg, then rhs, dinv, den, lambda
-template <int CH> struct RowLayout {
-  static constexpr int kJ = 6 + CH;
-  static constexpr int kRhs = kJ, kDinv = kJ + 1, kDen = kJ + 2, kLam = kJ + 3;
-  static constexpr int kRow = kJ + 4;
-  static constexpr int kContact = 3 * kRow + 1;   // n, t1, t2 rows + mu
-  static constexpr int kMu = 3 * kRow;
-};
-
 struct StepDiag {
   int32_t n_contacts, iterations;
 };
@@ -266,536 +264,6 @@ template <typename T, int N> SOLO_HD void chol_inverse_lower(T (&A)[N][N]) {
     }
 #pragma unroll
     for (int i = j; i < N; i++) A[i][j] = col[i];
-  }
-}
-
-// One Bullet-style physics step of cfg.dt for one environment.
-//   scratch: per-thread contact row storage, kMaxContacts * RowLayout<CH>::kContact
-//   cmd[l][j]: position target (POSITION_CONTROL) or torque (TORQUE)
-template <typename T, int CH>
-SOLO_HD void physics_step(const ModelT<T> &M, const ConfigT<T> &C, EnvState<T, CH> &s, const T (&cmd)[kLegs][CH],
-                          T *scratch, StepDiag *diag, const DebugOut<T> *dbg) {
-  typedef RowLayout<CH> RL;
-  const T dt = C.dt;
-
-  // ---------------- base kinematics ----------------
-  const M3<T> R0 = quat_to_mat(s.quat);
-  const V3<T> o0 = ld3(s.pos);
-  const V3<T> c0 = o0 + mul(R0, ld3(M.com[0]));
-  const V3<T> w0 = ld3(s.vang), vc0 = ld3(s.vlin);
-  const V3<T> grav = ld3(C.gravity);
-
-  // totals about c0: bias force/moment and composite inertia (mass, m*r, I_O)
-  V3<T> Ftot, Ntot;
-  T mtot = M.mass[0];
-  V3<T> htot = mk(T(0), T(0), T(0));
-  S3<T> Itot = rotate_inertia(R0, M.inertia[0]);
-  {
-    T vn = m_sqrt(dot(vc0, vc0)), wn = m_sqrt(dot(w0, w0));
-    V3<T> Iw = mul(Itot, w0);
-    V3<T> fext = grav * M.mass[0] - vc0 * (M.mass[0] * (C.lin_damp + C.lin_damp * vn));
-    V3<T> next = Iw * (-(C.ang_damp + C.ang_damp * wn));
-    Ftot = mk(T(0), T(0), T(0)) - fext;
-    Ntot = cross(w0, Iw) - next;
-  }
-
-  // Schur complement accumulator (full 6x6, lower part used) and reduced force
-  T S[6][6];
-#pragma unroll
-  for (int i = 0; i < 6; i++)
-#pragma unroll
-    for (int j = 0; j < 6; j++) S[i][j] = 0;
-  T gf[6] = {0, 0, 0, 0, 0, 0};  // sum_l Bh_l^T fh_l
-
-  // per-leg data kept for the row phase
-  V3<T> jo[kLegs][CH], ja[kLegs][CH];   // joint origin / axis, world
-  M3<T> jR[kLegs][CH];                  // body rotation
-  T E[kLegs][CH][CH];                   // C^-1 of the leg block (lower)
-  T Bh[kLegs][CH][6];                   // E B^T
-  T fh[kLegs][CH];                      // E f_leg
-
-#pragma unroll
-  for (int l = 0; l < kLegs; l++) {
-    V3<T> bc[CH], bw[CH], F[CH], N[CH];
-    S3<T> bI[CH];
-    T bm[CH];
-    bool act[CH];
-    {
-      M3<T> Rp = R0;
-      V3<T> op = o0, cp = c0, wp = w0, vcp = vc0;
-      V3<T> alp = mk(T(0), T(0), T(0)), accp = alp;
-#pragma unroll
-      for (int j = 0; j < CH; j++) {
-        act[j] = (l < M.n_legs) && (j < M.chain_len[l]);
-        const int d = act[j] ? M.dof0[l] + j : 0;
-        const int b = d + 1;
-        if (act[j]) {
-          const V3<T> ax = ld3(M.jaxis[d]);
-          M3<T> Jr;
-#pragma unroll
-          for (int k = 0; k < 9; k++) Jr.m[k] = M.jrot[d][k];
-          const M3<T> Rj = mul(mul(Rp, Jr), axis_angle(ax, s.q[l][j]));
-          const V3<T> oj = op + mul(Rp, ld3(M.jorigin[d]));
-          const V3<T> aj = mul(Rj, ax);
-          const V3<T> cj = oj + mul(Rj, ld3(M.com[b]));
-          const S3<T> Iw = rotate_inertia(Rj, M.inertia[b]);
-          const T qd = s.qd[l][j];
-          const V3<T> wj = wp + aj * qd;
-          const V3<T> rp = oj - cp, rc = cj - oj;
-          const V3<T> vo = vcp + cross(wp, rp);
-          const V3<T> vcj = vo + cross(wj, rc);
-          const V3<T> alj = alp + cross(wp, aj) * qd;
-          const V3<T> acco = accp + cross(alp, rp) + cross(wp, cross(wp, rp));
-          const V3<T> accc = acco + cross(alj, rc) + cross(wj, cross(wj, rc));
-          const T mass = M.mass[b];
-          const T vn = m_sqrt(dot(vcj, vcj)), wn = m_sqrt(dot(wj, wj));
-          const V3<T> Iww = mul(Iw, wj);
-          const V3<T> fext = grav * mass - vcj * (mass * (C.lin_damp + C.lin_damp * vn));
-          const V3<T> next = Iww * (-(C.ang_damp + C.ang_damp * wn));
-          F[j] = accc * mass - fext;
-          N[j] = mul(Iw, alj) + cross(wj, Iww) - next;
-          jo[l][j] = oj; ja[l][j] = aj; jR[l][j] = Rj;
-          bc[j] = cj; bw[j] = wj; bI[j] = Iw; bm[j] = mass;
-          Rp = Rj; op = oj; cp = cj; wp = wj; vcp = vcj; alp = alj; accp = accc;
-        } else {
-          jo[l][j] = o0; ja[l][j] = mk(T(0), T(0), T(0)); jR[l][j] = R0;
-          bc[j] = c0; bw[j] = w0; bm[j] = 0;
-          F[j] = mk(T(0), T(0), T(0)); N[j] = F[j];
-          bI[j].xx = bI[j].xy = bI[j].xz = bI[j].yy = bI[j].yz = bI[j].zz = 0;
-        }
-      }
-    }
-    // tip -> root: bias generalised forces and composite inertia
-    V3<T> Fs = mk(T(0), T(0), T(0)), Ns = Fs, ch = Fs;
-    T cm = 0;
-    S3<T> cI; cI.xx = cI.xy = cI.xz = cI.yy = cI.yz = cI.zz = 0;
-    V3<T> v0j[CH];   // linear velocity at c0 of a unit rate of joint j
-    V3<T> Bp[CH], BL[CH];
-    T D[CH][CH];
-    T fl[CH];
-#pragma unroll
-    for (int j = 0; j < CH; j++) v0j[j] = cross(ja[l][j], c0 - jo[l][j]);
-#pragma unroll
-    for (int j = CH - 1; j >= 0; j--) {
-      const V3<T> r = bc[j] - c0;
-      Fs = Fs + F[j];
-      Ns = Ns + cross(r, F[j]) + N[j];
-      const T Cj = dot(ja[l][j], Ns - cross(jo[l][j] - c0, Fs));
-      T tau = 0;
-      if (C.control_mode == 1) tau = m_clamp(cmd[l][j], -C.torque_limit, C.torque_limit);
-      fl[j] = act[j] ? tau - Cj : T(0);
-      const T mb = bm[j];
-      cm += mb;
-      ch = ch + r * mb;
-      const T rr = dot(r, r);
-      cI.xx += bI[j].xx + mb * (rr - r.x * r.x); cI.xy += bI[j].xy - mb * r.x * r.y;
-      cI.xz += bI[j].xz - mb * r.x * r.z;        cI.yy += bI[j].yy + mb * (rr - r.y * r.y);
-      cI.yz += bI[j].yz - mb * r.y * r.z;        cI.zz += bI[j].zz + mb * (rr - r.z * r.z);
-      const V3<T> p = v0j[j] * cm + cross(ja[l][j], ch);
-      const V3<T> L = mul(cI, ja[l][j]) + cross(ch, v0j[j]);
-      Bp[j] = p; BL[j] = L;
-#pragma unroll
-      for (int jj = 0; jj <= j; jj++) {
-        T v = dot(v0j[jj], p) + dot(ja[l][jj], L);
-        D[j][jj] = v; D[jj][j] = v;
-      }
-      if (!act[j]) D[j][j] = 1;   // dummy unit dof, zero coupling
-    }
-    Ftot = Ftot + Fs; Ntot = Ntot + Ns;
-    mtot += cm; htot = htot + ch;
-    Itot.xx += cI.xx; Itot.xy += cI.xy; Itot.xz += cI.xz; Itot.yy += cI.yy; Itot.yz += cI.yz; Itot.zz += cI.zz;
-    chol_inverse_lower<T, CH>(D);   // D <- C^-1 (lower)
-#pragma unroll
-    for (int i = 0; i < CH; i++) {
-#pragma unroll
-      for (int k = 0; k < CH; k++) E[l][i][k] = (k <= i) ? D[i][k] : T(0);
-      T b6[6] = {0, 0, 0, 0, 0, 0};
-      T f = 0;
-#pragma unroll
-      for (int k = 0; k <= i; k++) {
-        const T e = D[i][k];
-        b6[0] += e * Bp[k].x; b6[1] += e * Bp[k].y; b6[2] += e * Bp[k].z;
-        b6[3] += e * BL[k].x; b6[4] += e * BL[k].y; b6[5] += e * BL[k].z;
-        f += e * fl[k];
-      }
-      fh[l][i] = f;
-#pragma unroll
-      for (int a = 0; a < 6; a++) {
-        Bh[l][i][a] = b6[a];
-        gf[a] += b6[a] * f;
-#pragma unroll
-        for (int b = 0; b <= a; b++) S[a][b] -= b6[a] * b6[b];
-      }
-    }
-  }
-
-  // ---------------- base Schur complement ----------------
-  S[0][0] += mtot; S[1][1] += mtot; S[2][2] += mtot;
-  // lin-ang block: p = m v + w x h  ->  row x: (0, hz, -hy) etc.; lower part = its transpose
-  S[3][1] += -htot.z; S[3][2] += htot.y;
-  S[4][0] += htot.z;  S[4][2] += -htot.x;
-  S[5][0] += -htot.y; S[5][1] += htot.x;
-  S[3][3] += Itot.xx; S[4][3] += Itot.xy; S[5][3] += Itot.xz;
-  S[4][4] += Itot.yy; S[5][4] += Itot.yz; S[5][5] += Itot.zz;
-  chol_inverse_lower<T, 6>(S);   // S <- Ls (lower)
-
-  // ---------------- unconstrained acceleration, v += a dt ----------------
-  T vb[6] = {s.vlin[0], s.vlin[1], s.vlin[2], s.vang[0], s.vang[1], s.vang[2]};
-  T vl[kLegs][CH];
-  {
-    T g[6] = {-Ftot.x - gf[0], -Ftot.y - gf[1], -Ftot.z - gf[2], -Ntot.x - gf[3], -Ntot.y - gf[4], -Ntot.z - gf[5]};
-    T fb[6], ab[6];
-#pragma unroll
-    for (int i = 0; i < 6; i++) {
-      T t = 0;
-#pragma unroll
-      for (int k = 0; k <= i; k++) t += S[i][k] * g[k];
-      fb[i] = t;
-    }
-#pragma unroll
-    for (int i = 0; i < 6; i++) {
-      T t = 0;
-#pragma unroll
-      for (int k = i; k < 6; k++) t += S[k][i] * fb[k];
-      ab[i] = t;
-      vb[i] = m_clamp(vb[i] + t * dt, -C.max_vel, C.max_vel);
-    }
-#pragma unroll
-    for (int l = 0; l < kLegs; l++) {
-      T t[CH];
-#pragma unroll
-      for (int i = 0; i < CH; i++) {
-        T u = fh[l][i];
-#pragma unroll
-        for (int a = 0; a < 6; a++) u -= Bh[l][i][a] * ab[a];
-        t[i] = u;
-      }
-#pragma unroll
-      for (int i = 0; i < CH; i++) {
-        T acc = 0;
-#pragma unroll
-        for (int k = i; k < CH; k++) acc += E[l][k][i] * t[k];
-        vl[l][i] = m_clamp(s.qd[l][i] + acc * dt, -C.max_vel, C.max_vel);
-      }
-    }
-  }
-
-  // ---------------- motor rows (POSITION_CONTROL) ----------------
-  const bool motors = (C.control_mode == 0);
-  T mrow[kLegs][CH][RL::kRow];
-  if (motors) {
-#pragma unroll
-    for (int l = 0; l < kLegs; l++)
-#pragma unroll
-      for (int i = 0; i < CH; i++) {
-        T *r = mrow[l][i];
-        T g[6] = {0, 0, 0, 0, 0, 0};
-        T den = 0;
-#pragma unroll
-        for (int k = 0; k < CH; k++) {
-          const T e = (k >= i) ? E[l][k][i] : T(0);
-          r[6 + k] = e;
-          den += e * e;
-#pragma unroll
-          for (int a = 0; a < 6; a++) g[a] -= Bh[l][k][a] * e;
-        }
-#pragma unroll
-        for (int a = 0; a < 6; a++) {
-          T t = 0;
-#pragma unroll
-          for (int k = 0; k <= a; k++) t += S[a][k] * g[k];
-          r[a] = t;
-          den += t * t;
-        }
-        const T dinv = T(1) / den;
-        r[RL::kDen] = den; r[RL::kDinv] = dinv;
-        // btMultiBodyJointMotor: velocity error kp (q* - q)/dt - kd v
-        r[RL::kRhs] = (C.kp * (cmd[l][i] - s.q[l][i]) * C.inv_dt - C.kd * vl[l][i]) * dinv;
-        r[RL::kLam] = 0;
-      }
-  }
-
-  // ---------------- contact rows ----------------
-  int nc = 0;
-  int leg_end[kLegs + 1];   // contact index ranges: [0, leg_end[0]) base, then per leg
-  int ccand[kMaxContacts];
-  auto add_contacts = [&](const int body, const int l, const int depth, const V3<T> ob, const M3<T> &Rb) {
-    for (int c = M.cand_begin[body]; c < M.cand_begin[body + 1]; c++) {
-      const V3<T> p = ob + mul(Rb, ld3(M.cand_pos[c]));
-      const T dist = p.z - M.margin;
-      if (!(dist < C.breaking) || nc >= C.max_contacts) continue;
-      T *row = scratch + nc * RL::kContact;
-      ccand[nc] = c;
-      const V3<T> pc = mk(p.x, p.y, dist);
-      const V3<T> r = pc - c0;
-      V3<T> vp = mk(vb[0], vb[1], vb[2]) + cross(mk(vb[3], vb[4], vb[5]), r);
-      V3<T> w[CH];
-#pragma unroll
-      for (int j = 0; j < CH; j++) {
-        if (l >= 0 && j <= depth) {
-          w[j] = cross(ja[l < 0 ? 0 : l][j], pc - jo[l < 0 ? 0 : l][j]);
-          vp = vp + w[j] * vl[l < 0 ? 0 : l][j];
-        } else {
-          w[j] = mk(T(0), T(0), T(0));
-        }
-      }
-      // directions: n = +z, t1 = -y, t2 = +x  (btPlaneSpace1 of (0,0,1))
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        T *o = row + k * RL::kRow;
-        T g[6], jl[CH];
-        if (k == 0) {
-          g[0] = 0; g[1] = 0; g[2] = 1; g[3] = r.y; g[4] = -r.x; g[5] = 0;
-#pragma unroll
-          for (int j = 0; j < CH; j++) jl[j] = w[j].z;
-        } else if (k == 1) {
-          g[0] = 0; g[1] = -1; g[2] = 0; g[3] = r.z; g[4] = 0; g[5] = -r.x;
-#pragma unroll
-          for (int j = 0; j < CH; j++) jl[j] = -w[j].y;
-        } else {
-          g[0] = 1; g[1] = 0; g[2] = 0; g[3] = 0; g[4] = r.z; g[5] = -r.y;
-#pragma unroll
-          for (int j = 0; j < CH; j++) jl[j] = w[j].x;
-        }
-        T den = 0;
-        if (l >= 0) {
-          const int ll = l < 0 ? 0 : l;
-#pragma unroll
-          for (int i = 0; i < CH; i++) {
-            T t = 0;
-#pragma unroll
-            for (int kk = 0; kk <= i; kk++) t += E[ll][i][kk] * jl[kk];
-            o[6 + i] = t;
-            den += t * t;
-#pragma unroll
-            for (int a = 0; a < 6; a++) g[a] -= Bh[ll][i][a] * t;
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < CH; i++) o[6 + i] = 0;
-        }
-#pragma unroll
-        for (int a = 0; a < 6; a++) {
-          T t = 0;
-#pragma unroll
-          for (int kk = 0; kk <= a; kk++) t += S[a][kk] * g[kk];
-          o[a] = t;
-          den += t * t;
-        }
-        const T dinv = T(1) / den;
-        o[RL::kDen] = den; o[RL::kDinv] = dinv; o[RL::kLam] = 0;
-        if (k == 0) {
-          const T pen = dist + C.slop;
-          T err = -vp.z;   // restitution 0
-          if (pen > 0) err -= pen * C.inv_dt; else err += -pen * C.erp * C.inv_dt;
-          o[RL::kRhs] = err * dinv;
-        } else {
-          const T rel = (k == 1) ? -vp.y : vp.x;
-          o[RL::kRhs] = -rel * dinv;
-        }
-      }
-      row[RL::kMu] = M.cand_mu[c];
-      nc++;
-    }
-  };
-  add_contacts(0, -1, 0, o0, R0);
-  leg_end[0] = nc;
-#pragma unroll
-  for (int l = 0; l < kLegs; l++) {
-#pragma unroll
-    for (int j = 0; j < CH; j++) {
-      if ((l < M.n_legs) && (j < M.chain_len[l])) add_contacts(M.dof0[l] + j + 1, l, j, jo[l][j], jR[l][j]);
-    }
-    leg_end[l + 1] = nc;
-  }
-
-  // ---------------- PGS (btMultiBodyConstraintSolver::solveSingleIteration order) ----------------
-  T yb[6] = {0, 0, 0, 0, 0, 0};
-  T yl[kLegs][CH];
-#pragma unroll
-  for (int l = 0; l < kLegs; l++)
-#pragma unroll
-    for (int i = 0; i < CH; i++) yl[l][i] = 0;
-  const T mlim = C.torque_limit * dt;
-  int it = 0;
-  if (motors || nc > 0) {
-    for (; it < C.iters;) {
-      T res = 0;
-      if (motors) {
-        // direction of traversal alternates with iteration parity (odd: forward)
-        auto motor = [&](const int l, const int i) {
-          if (!((l < M.n_legs) && (i < M.chain_len[l]))) return;
-          T *r = mrow[l][i];
-          T jdv = 0;
-#pragma unroll
-          for (int a = 0; a < 6; a++) jdv += r[a] * yb[a];
-#pragma unroll
-          for (int k = 0; k < CH; k++) jdv += r[6 + k] * yl[l][k];
-          T delta = r[RL::kRhs] - jdv * r[RL::kDinv];
-          const T lam = r[RL::kLam];
-          T sum = lam + delta;
-          if (sum < -mlim) { delta = -mlim - lam; sum = -mlim; }
-          else if (sum > mlim) { delta = mlim - lam; sum = mlim; }
-          r[RL::kLam] = sum;
-#pragma unroll
-          for (int a = 0; a < 6; a++) yb[a] += r[a] * delta;
-#pragma unroll
-          for (int k = 0; k < CH; k++) yl[l][k] += r[6 + k] * delta;
-          const T rr = delta * r[RL::kDen];
-          res = m_max(res, rr * rr);
-        };
-        if (it & 1) {
-#pragma unroll
-          for (int jj = 0; jj < kLegs * CH; jj++) motor(jj / CH, jj % CH);
-        } else {
-#pragma unroll
-          for (int jj = kLegs * CH - 1; jj >= 0; jj--) motor(jj / CH, jj % CH);
-        }
-      }
-      // normal rows
-#pragma unroll
-      for (int g = 0; g <= kLegs; g++) {
-        const int l = g - 1;
-        for (int c = (g == 0 ? 0 : leg_end[g - 1]); c < leg_end[g]; c++) {
-          T *r = scratch + c * RL::kContact;
-          T jdv = 0;
-#pragma unroll
-          for (int a = 0; a < 6; a++) jdv += r[a] * yb[a];
-          if (g > 0) {
-#pragma unroll
-            for (int k = 0; k < CH; k++) jdv += r[6 + k] * yl[l < 0 ? 0 : l][k];
-          }
-          T delta = r[RL::kRhs] - jdv * r[RL::kDinv];
-          const T lam = r[RL::kLam];
-          T sum = lam + delta;
-          if (sum < 0) { delta = -lam; sum = 0; }
-          r[RL::kLam] = sum;
-#pragma unroll
-          for (int a = 0; a < 6; a++) yb[a] += r[a] * delta;
-          if (g > 0) {
-#pragma unroll
-            for (int k = 0; k < CH; k++) yl[l < 0 ? 0 : l][k] += r[6 + k] * delta;
-          }
-          const T rr = delta * r[RL::kDen];
-          res = m_max(res, rr * rr);
-        }
-      }
-      // friction pairs (resolveConeFrictionConstraintRows: both rows on the same
-      // dv, radial projection onto the disc of radius mu * lambda_n)
-#pragma unroll
-      for (int g = 0; g <= kLegs; g++) {
-        const int l = g - 1;
-        for (int c = (g == 0 ? 0 : leg_end[g - 1]); c < leg_end[g]; c++) {
-          T *rn = scratch + c * RL::kContact;
-          T *ra = rn + RL::kRow, *rb = rn + 2 * RL::kRow;
-          T ja_ = 0, jb_ = 0;
-#pragma unroll
-          for (int a = 0; a < 6; a++) { ja_ += ra[a] * yb[a]; jb_ += rb[a] * yb[a]; }
-          if (g > 0) {
-#pragma unroll
-            for (int k = 0; k < CH; k++) {
-              ja_ += ra[6 + k] * yl[l < 0 ? 0 : l][k];
-              jb_ += rb[6 + k] * yl[l < 0 ? 0 : l][k];
-            }
-          }
-          const T la = ra[RL::kLam], lb = rb[RL::kLam];
-          T sa = la + (ra[RL::kRhs] - ja_ * ra[RL::kDinv]);
-          T sb = lb + (rb[RL::kRhs] - jb_ * rb[RL::kDinv]);
-          const T limit = rn[RL::kMu] * rn[RL::kLam];
-          const T n2 = sa * sa + sb * sb;
-          if (n2 > limit * limit) {
-            const T sc = limit / m_sqrt(n2);
-            sa *= sc; sb *= sc;
-          }
-          const T da = sa - la, db = sb - lb;
-          ra[RL::kLam] = sa; rb[RL::kLam] = sb;
-#pragma unroll
-          for (int a = 0; a < 6; a++) yb[a] += ra[a] * da + rb[a] * db;
-          if (g > 0) {
-#pragma unroll
-            for (int k = 0; k < CH; k++) yl[l < 0 ? 0 : l][k] += ra[6 + k] * da + rb[6 + k] * db;
-          }
-          const T r1 = da * ra[RL::kDen], r2 = db * rb[RL::kDen];
-          res = m_max(res, m_max(r1 * r1, r2 * r2));
-        }
-      }
-      it++;
-      if (res <= C.res_thr) break;
-    }
-  }
-
-  // ---------------- dv = T^T yh, integrate ----------------
-  T dvb[6];
-#pragma unroll
-  for (int i = 0; i < 6; i++) {
-    T t = 0;
-#pragma unroll
-    for (int k = i; k < 6; k++) t += S[k][i] * yb[k];
-    dvb[i] = t;
-    vb[i] = m_clamp(vb[i] + t, -C.max_vel, C.max_vel);
-  }
-#pragma unroll
-  for (int l = 0; l < kLegs; l++) {
-    T t[CH];
-#pragma unroll
-    for (int i = 0; i < CH; i++) {
-      T u = yl[l][i];
-#pragma unroll
-      for (int a = 0; a < 6; a++) u -= Bh[l][i][a] * dvb[a];
-      t[i] = u;
-    }
-#pragma unroll
-    for (int i = 0; i < CH; i++) {
-      T dv = 0;
-#pragma unroll
-      for (int k = i; k < CH; k++) dv += E[l][k][i] * t[k];
-      const bool a = (l < M.n_legs) && (i < M.chain_len[l]);
-      const T v = a ? m_clamp(vl[l][i] + dv, -C.max_vel, C.max_vel) : T(0);
-      s.qd[l][i] = v;
-      s.q[l][i] += dt * v;
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    s.vlin[i] = vb[i];
-    s.vang[i] = vb[3 + i];
-    s.pos[i] += dt * vb[i];
-  }
-  {
-    // base orientation: exponential map of the world angular velocity
-    // (btTransformUtil::integrateTransform as used by stepPositionsMultiDof)
-    const T wx = vb[3], wy = vb[4], wz = vb[5];
-    T ang = m_sqrt(wx * wx + wy * wy + wz * wz);
-    if (ang * dt > T(0.25 * 3.14159265358979323846)) ang = T(0.5 * 0.5 * 3.14159265358979323846) / dt;
-    T sc, cs, sn;
-    m_sincos(T(0.5) * ang * dt, &sn, &cs);
-    if (ang < T(0.001)) sc = T(0.5) * dt - dt * dt * dt * T(0.020833333333) * ang * ang;
-    else sc = sn / ang;
-    const T dx = wx * sc, dy = wy * sc, dz = wz * sc, dw = cs;
-    const T x = s.quat[0], y = s.quat[1], z = s.quat[2], w = s.quat[3];
-    T nx = dw * x + dx * w + dy * z - dz * y;
-    T ny = dw * y - dx * z + dy * w + dz * x;
-    T nz = dw * z + dx * y - dy * x + dz * w;
-    T nw = dw * w - dx * x - dy * y - dz * z;
-    const T nn = T(1) / m_sqrt(nx * nx + ny * ny + nz * nz + nw * nw);
-    s.quat[0] = nx * nn; s.quat[1] = ny * nn; s.quat[2] = nz * nn; s.quat[3] = nw * nn;
-  }
-
-  if (diag) { diag->n_contacts = nc; diag->iterations = it; }
-  if (dbg) {
-    if (dbg->normal_force) {
-      for (int c = 0; c < M.n_cand; c++) dbg->normal_force[c * dbg->stride] = 0;
-      for (int i = 0; i < nc; i++)
-        dbg->normal_force[ccand[i] * dbg->stride] = scratch[i * RL::kContact + RL::kLam] * C.inv_dt;
-    }
-    if (dbg->motor_torque) {
-#pragma unroll
-      for (int l = 0; l < kLegs; l++)
-#pragma unroll
-        for (int i = 0; i < CH; i++)
-          if ((l < M.n_legs) && (i < M.chain_len[l]))
-            dbg->motor_torque[(M.dof0[l] + i) * dbg->stride] = motors ? mrow[l][i][RL::kLam] * C.inv_dt : T(0);
-    }
   }
 }
 

@@ -1,27 +1,37 @@
 // solo_kernels.cuh -- sm_100a kernels of the Solo 8 env-step path.
 //
-// One thread per environment.  The per-environment arithmetic is
-// solo_core.h (float32); this file adds the batched memory plan:
-//   * constant tables (model, config, epilogue program) travel as ONE
-//     __grid_constant__ kernel parameter, i.e. they sit in the constant bank
-//     and every warp-uniform read is an LDC / direct FFMA operand -- no staging
-//     loop, no shared-memory bank traffic, and no module-global state, so two
-//     handles with different robots can coexist in one process;
-//   * state is structure-of-arrays state[field][env]: every load/store of a
-//     field is one fully coalesced 128 B line per warp, exactly once per
-//     env.step (read at entry, written at exit; substeps stay in registers);
-//   * actions arrive and observations leave in the reference's [env][k] layout
-//     (solo8v2vanilla.py:72-102) and are transposed through shared memory so
-//     that the global side is again whole lines;
-//   * the contact rows of the PGS sweep live in thread-local memory, which the
-//     hardware interleaves per lane (row i of 32 envs = 32 consecutive words).
+// One env.step = three launches on the caller's stream (solo_phases.h):
+//
+//   setup_kernel   one thread per environment.  Reads the action tile and the
+//                  SoA state, runs the articulated-body setup, writes the
+//                  constraint rows [env][slot][kRow] (48/64-byte records, one
+//                  contiguous list per environment so that the solver walks
+//                  consecutive cache lines), the mass-matrix
+//                  factors [k][env] and the per-env contact header.
+//   solve_kernel   the data-dependent part: projected Gauss-Seidel, a serial
+//                  chain of 8 + 3 n_contacts row updates x 2..50 iterations per
+//                  environment.  Environments are spread `lanes` per warp so
+//                  that a small batch still covers every SM sub-partition and a
+//                  warp only waits for the slowest of `lanes` environments.
+//                  Rows stream from L1/L2 one update ahead; impulses live in
+//                  shared memory; yh in registers.
+//   finish_kernel  one thread per environment: dv = T^T yh, integration, NaN
+//                  guard, observations, reward, termination, optional snapshot
+//                  auto-reset; writes the SoA state and the [env][k] outputs
+//                  (transposed through shared memory into whole lines).
+//
+// Constant tables (model, config, epilogue program) travel as ONE
+// __grid_constant__ kernel parameter: warp-uniform reads are LDC / direct FFMA
+// operands, there is no module-global state, and handles with different robots
+// coexist in one process.  Intermediates (rows, factors, yh) live in the
+// caller-bound scratch and stay L2-resident for the batch sizes of the bench.
 #ifndef SOLO_KERNELS_CUH_
 #define SOLO_KERNELS_CUH_
 
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include "solo_core.h"
+#include "solo_phases.h"
 
 namespace solo {
 
@@ -37,18 +47,18 @@ struct Buffers {
   int32_t *counters;         // [kMaxTermTerms][n]
   const float *snapshot;     // [state_dim]
   float *stats;              // [4][n] or null: running return, running length, last return, episodes
-  unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, env-steps
+  unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, physics steps
   float *dbg_normal_force;   // [n_cand][n] or null
   float *dbg_motor_torque;   // [ndof][n] or null
+  // solver scratch (caller-bound, solo_scratch_bytes)
+  const float *cand_tab;     // [n_cand][4] support point xyz + friction
+  uint32_t *hdr;             // [2][n] contact-group ends, contact count
+  float *yh;                 // [6 + kLegs * CH][n]
+  float *fac;                // [FactorLayout<CH>::kSize][n]
+  float *rows;               // [n][RowLayout<CH>::kSlots][kRow]: one contiguous record list per env
   int32_t n;
   int32_t obs_dim;
 };
-
-__device__ __forceinline__ bool state_finite(const float *p, int n) {
-  float acc = 0.f;
-  for (int i = 0; i < n; i++) acc += p[i] * 0.f;   // NaN/Inf propagate, finite -> 0
-  return acc == 0.f;
-}
 
 template <int CH>
 __device__ __forceinline__ bool env_finite(const EnvState<float, CH> &s) {
@@ -61,7 +71,7 @@ __device__ __forceinline__ bool env_finite(const EnvState<float, CH> &s) {
   for (int l = 0; l < kLegs; l++)
 #pragma unroll
     for (int j = 0; j < CH; j++) acc += (s.q[l][j] + s.qd[l][j]) * 0.f;
-  return acc == 0.f;
+  return acc == 0.f;   // NaN/Inf propagate, finite -> 0
 }
 
 template <int CH>
@@ -69,8 +79,8 @@ __device__ __forceinline__ void load_snapshot(const ModelT<float> &M, const floa
   load_state<float, CH, float>(M, snap, 1, s);
 }
 
+// warp-level reduction, one atomic per warp and counter
 __device__ __forceinline__ void diag_add(unsigned long long *diag, int contacts, int iters, int nan, int steps) {
-  // warp-level reduction, one atomic per warp and counter
   const unsigned mask = __activemask();
   for (int off = 16; off > 0; off >>= 1) {
     contacts += __shfl_down_sync(mask, contacts, off);
@@ -79,17 +89,15 @@ __device__ __forceinline__ void diag_add(unsigned long long *diag, int contacts,
     steps += __shfl_down_sync(mask, steps, off);
   }
   if ((threadIdx.x & 31) == 0) {
-    atomicAdd(diag + 0, (unsigned long long)contacts);
-    atomicAdd(diag + 1, (unsigned long long)iters);
+    if (contacts) atomicAdd(diag + 0, (unsigned long long)contacts);
+    if (iters) atomicAdd(diag + 1, (unsigned long long)iters);
     if (nan) atomicAdd(diag + 2, (unsigned long long)nan);
-    atomicAdd(diag + 3, (unsigned long long)steps);
+    if (steps) atomicAdd(diag + 3, (unsigned long long)steps);
   }
 }
 
 // Block-cooperative transpose of a [rows = blockDim.x envs][k] tile between the
 // reference's row-major layout in global memory and one value per thread.
-//   gather : tile[t][j] (global, row-major, contiguous) -> smem, then thread t reads its row
-//   scatter: thread t writes its row to smem, then the tile is stored contiguous
 // smem holds blockDim.x * k floats; rows are padded to an odd stride to keep the
 // per-thread row accesses conflict free.
 __device__ __forceinline__ int pad_stride(int k) { return k | 1; }
@@ -118,54 +126,143 @@ __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0
 }
 
 // ---------------------------------------------------------------------------------
-// env.step for every env (solo8v2vanilla.py:72-102)
+// phase 1: setJointMotorControlArray + the pre-solver half of stepSimulation
+// (solo8v2vanilla.py:87-91)
 // ---------------------------------------------------------------------------------
-template <int CH, bool DBG>
+template <int CH>
 __global__ void __launch_bounds__(128)
-step_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__restrict__ actions,
-            const float action_scale, float *__restrict__ obs_out, float *__restrict__ reward_out,
-            uint8_t *__restrict__ done_out, float *__restrict__ terminal_obs_out) {
+setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__restrict__ actions,
+             const int broadcast, const float action_scale) {
   extern __shared__ float smem[];
+  typedef RowLayout<CH> RL;
   const ModelT<float> &M = K.M;
-  const ConfigT<float> &C = K.C;
-  const ProgramC &P = K.P;
   const int64_t env0 = (int64_t)blockIdx.x * blockDim.x;
   const int64_t env = env0 + threadIdx.x;
   const int n_valid = (int)min((int64_t)blockDim.x, (int64_t)B.n - env0);
   const bool live = env < B.n;
   const int n_api = M.n_api;
 
-  // actions: [env][n_api] -> per-thread command
-  tile_gather(actions, env0, n_valid, n_api, smem);
   float cmd[kLegs][CH];
-  if (live) load_command<float, CH, float>(M, smem + threadIdx.x * pad_stride(n_api), action_scale, cmd);
-  __syncthreads();   // smem is reused for the observation tile below
+  if (broadcast) {
+    load_command<float, CH, float>(M, actions, action_scale, cmd);
+  } else {
+    // actions: [env][n_api] -> per-thread command
+    tile_gather(actions, env0, n_valid, n_api, smem);
+    if (live) load_command<float, CH, float>(M, smem + threadIdx.x * pad_stride(n_api), action_scale, cmd);
+  }
+  if (!live) return;
+  EnvState<float, CH> s;
+  load_state<float, CH, float>(M, B.state + env, B.n, s);
+  const RowHeader h = setup_step<float, CH>(M, K.C, s, cmd, B.cand_tab, B.rows + env * (RL::kSlots * RL::kRow),
+                                            RL::kRow, B.fac + env, B.n);
+  B.hdr[env] = h.ends03;
+  B.hdr[(int64_t)B.n + env] = h.nc;
+}
+
+// ---------------------------------------------------------------------------------
+// phase 2: the constraint solver of stepSimulation.  One warp per block; lanes
+// [0, lanes) of warp w own environments w * lanes + lane.
+// ---------------------------------------------------------------------------------
+template <int CH, bool DBG>
+__global__ void __launch_bounds__(32)
+solve_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const uint32_t motor_mask, const int lanes,
+             const int ndof_total, const int n_cand) {
+  extern __shared__ float lam_sm[];   // [3 * kMaxContacts][lanes]
+  typedef RowLayout<CH> RL;
+  const int lane = threadIdx.x;
+  const int64_t env = (int64_t)blockIdx.x * lanes + lane;
+  const bool live = lane < lanes && env < B.n;
+  int contacts = 0, iters = 0;
+  if (live) {
+    RowHeader h;
+    h.ends03 = B.hdr[env];
+    h.nc = B.hdr[(int64_t)B.n + env];
+    float yb[6], yl[kLegs][CH], mlam[kLegs * CH];
+    const float *rows = B.rows + env * (RL::kSlots * RL::kRow);
+    const int64_t slot_stride = RL::kRow;
+    iters = solve_rows<float, CH>(C, motor_mask, rows, slot_stride, h, lam_sm + lane, lanes, yb, yl, mlam);
+    contacts = (int)h.nc;
+    float *y = B.yh + env;
+#pragma unroll
+    for (int a = 0; a < 6; a++) y[(int64_t)a * B.n] = yb[a];
+#pragma unroll
+    for (int l = 0; l < kLegs; l++)
+#pragma unroll
+      for (int k = 0; k < CH; k++) y[(int64_t)(6 + l * CH + k) * B.n] = yl[l][k];
+    if (DBG) {
+      if (B.dbg_normal_force) {
+        for (int c = 0; c < n_cand; c++) B.dbg_normal_force[(int64_t)c * B.n + env] = 0.f;
+        for (int i = 0; i < (int)h.nc; i++) {
+          const float *nr = rows + (int64_t)(RL::kMotorSlots + 3 * i) * slot_stride;
+          B.dbg_normal_force[(int64_t)(int)nr[RL::kX] * B.n + env] = lam_sm[(3 * i) * lanes + lane] * nr[RL::kIs] * C.inv_dt;
+        }
+      }
+      if (B.dbg_motor_torque) {
+        // dof order == (leg, joint) order with inactive slots skipped
+        int d = 0;
+        if (motor_mask == 0)
+          for (int k = 0; k < ndof_total; k++) B.dbg_motor_torque[(int64_t)k * B.n + env] = 0.f;
+#pragma unroll
+        for (int j = 0; j < kLegs * CH; j++) {
+          if ((motor_mask >> j) & 1u) {
+            const float *mr = rows + (int64_t)j * slot_stride;
+            if (d < ndof_total) B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * mr[RL::kIs] * C.inv_dt;
+            d++;
+          }
+        }
+      }
+    }
+  }
+  if (B.diag) diag_add(B.diag, contacts, iters, 0, live ? 1 : 0);
+}
+
+// ---------------------------------------------------------------------------------
+// phase 3: velocity update + integration, then (epilogue != 0) the rest of
+// env.step (solo8v2vanilla.py:96-102): observations, reward, termination,
+// optional in-kernel auto reset.
+// ---------------------------------------------------------------------------------
+template <int CH>
+__global__ void __launch_bounds__(128)
+finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epilogue, float *__restrict__ obs_out,
+              float *__restrict__ reward_out, uint8_t *__restrict__ done_out, float *__restrict__ terminal_obs_out) {
+  extern __shared__ float smem[];
+  const ModelT<float> &M = K.M;
+  const ProgramC &P = K.P;
+  const int64_t env0 = (int64_t)blockIdx.x * blockDim.x;
+  const int64_t env = env0 + threadIdx.x;
+  const int n_valid = (int)min((int64_t)blockDim.x, (int64_t)B.n - env0);
+  const bool live = env < B.n;
 
   EnvState<float, CH> s;
   float ob[kMaxObsDim];
   float rew = 0.f;
   bool done = false;
-  int contacts = 0, iters = 0, nan = 0;
+  int nan = 0;
   if (live) {
     load_state<float, CH, float>(M, B.state + env, B.n, s);
-    float scratch[kMaxContacts * RowLayout<CH>::kContact];
-    DebugOut<float> dbg;
-    dbg.normal_force = DBG && B.dbg_normal_force ? B.dbg_normal_force + env : nullptr;
-    dbg.motor_torque = DBG && B.dbg_motor_torque ? B.dbg_motor_torque + env : nullptr;
-    dbg.stride = B.n;
-    for (int k = 0; k < C.substeps; k++) {
-      StepDiag d;
-      physics_step<float, CH>(M, C, s, cmd, scratch, &d, DBG ? &dbg : nullptr);
-      contacts += d.n_contacts; iters += d.iterations;
-    }
+    float yb[6], yl[kLegs][CH];
+    const float *y = B.yh + env;
+#pragma unroll
+    for (int a = 0; a < 6; a++) yb[a] = y[(int64_t)a * B.n];
+#pragma unroll
+    for (int l = 0; l < kLegs; l++)
+#pragma unroll
+      for (int k = 0; k < CH; k++) yl[l][k] = y[(int64_t)(6 + l * CH + k) * B.n];
+    finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
     if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
+  }
+  if (!epilogue) {
+    if (live) store_state<float, CH, float>(M, s, B.state + env, B.n);
+    if (B.diag && nan) atomicAdd(B.diag + 2, 1ull);
+    return;
+  }
 
+  if (live) {
     float e[3];
     euler_from_quat(s.quat, e);
     compute_obs<float, CH>(M, P, s, e, ob);
     rew = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
     done = eval_terminations(P, B.counters + env, B.n);
-
     if (B.stats) {
       float ret = B.stats[env] + rew;
       float len = B.stats[(int64_t)B.n + env] + 1.f;
@@ -205,40 +302,7 @@ step_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__r
     for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
   }
   tile_scatter(obs_out, env0, n_valid, od, smem);
-  if (B.diag) diag_add(B.diag, contacts, iters, nan, live ? 1 : 0);
-}
-
-// ---------------------------------------------------------------------------------
-// setJointMotorControlArray + stepSimulation, n_steps times with one command
-// (solo8v2vanilla.py:87-91; the 500 settle steps of reset :130-136).  State stays
-// in registers across the steps.
-// ---------------------------------------------------------------------------------
-template <int CH, bool DBG>
-__global__ void __launch_bounds__(128)
-simulate_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__restrict__ actions,
-                const int broadcast, const int n_steps) {
-  const ModelT<float> &M = K.M;
-  const ConfigT<float> &C = K.C;
-  const int64_t env = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (env >= B.n) return;
-  float cmd[kLegs][CH];
-  load_command<float, CH, float>(M, actions + (broadcast ? 0 : env * M.n_api), 1.f, cmd);
-  EnvState<float, CH> s;
-  load_state<float, CH, float>(M, B.state + env, B.n, s);
-  float scratch[kMaxContacts * RowLayout<CH>::kContact];
-  DebugOut<float> dbg;
-  dbg.normal_force = DBG && B.dbg_normal_force ? B.dbg_normal_force + env : nullptr;
-  dbg.motor_torque = DBG && B.dbg_motor_torque ? B.dbg_motor_torque + env : nullptr;
-  dbg.stride = B.n;
-  int contacts = 0, iters = 0, nan = 0;
-  for (int k = 0; k < n_steps; k++) {
-    StepDiag d;
-    physics_step<float, CH>(M, C, s, cmd, scratch, &d, DBG ? &dbg : nullptr);
-    contacts += d.n_contacts; iters += d.iterations;
-  }
-  if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
-  store_state<float, CH, float>(M, s, B.state + env, B.n);
-  if (B.diag) diag_add(B.diag, contacts, iters, nan, n_steps);
+  if (B.diag && nan) atomicAdd(B.diag + 2, 1ull);
 }
 
 // obs_factory.get_obs() / reward_factory.get_reward() on the current state

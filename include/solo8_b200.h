@@ -156,7 +156,8 @@ int solo_destroy(SoloHandle h);
 int solo_set_program(SoloHandle h, const SoloProgram *program);
 /* len(observation_space.low) for the current program (obs.py:161-190). */
 int solo_obs_dim(SoloHandle h);
-/* Bytes of per-env scratch the caller must bind (0 if none). */
+/* Bytes of solver scratch the caller must bind (256-byte aligned): constraint
+ * rows, mass-matrix factors, solver output and contact headers of one step. */
 int64_t solo_scratch_bytes(SoloHandle h);
 
 /* Bind caller-owned device buffers.  state_dev: float[SOLO_STATE_DIM][n_envs];
@@ -213,8 +214,17 @@ int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
  * dof (float[ndof][n_envs], == getJointState()[3]) of the last physics step.
  * NULL disables; binding either selects the instrumented kernel variant. */
 int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev);
-/* Threads per block the handle launches with (one thread per environment). */
+/* Threads per block of the one-thread-per-environment kernels (setup, finish). */
 int solo_block_size(SoloHandle h);
+/* Environments per warp in the solver kernel (SOLO_LANES overrides). */
+int solo_solver_lanes(SoloHandle h);
+/* Live per-kernel timing (bench.py roofline): while enabled every physics step
+ * records CUDA events on the launching stream around its three kernels;
+ * solo_phase_times synchronises on them and returns the number of physics
+ * steps timed since enabling, with the summed setup / solve / finish
+ * milliseconds in ms3[0..2]. */
+int solo_phase_timing(SoloHandle h, int32_t enable);
+int64_t solo_phase_times(SoloHandle h, double *ms3);
 /* How many kernels this handle has launched so far (bench `gpu_launches`). */
 int64_t solo_launch_count(SoloHandle h);
 const char *solo_last_error(SoloHandle h);

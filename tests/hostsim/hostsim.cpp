@@ -21,7 +21,7 @@ static int run_step(const SoloModel *m, const SoloConfig *c, double *state, cons
   load_state<T, CH, double>(M, state, 1, s);
   T cmd[kLegs][CH];
   load_command<T, CH, double>(M, action, T(1), cmd);
-  std::vector<T> scratch((size_t)kMaxContacts * RowLayout<CH>::kContact);
+  std::vector<T> scratch((size_t)HostScratch<T, CH>::kSize);
   std::vector<T> nf(kMaxCand), mt(kMaxDof);
   DebugOut<T> dbg = {nf.data(), mt.data(), 1};
   StepDiag d = {0, 0};

@@ -1,0 +1,79 @@
+"""The CUDA kernels' per-environment core (gym_solo_b200/csrc/solo_phases.h:
+setup_step -> solve_rows -> finish_step) compiled for the host (tests/hostsim)
+against the oracle.  No GPU needed: this pins the kernel ARITHMETIC on CPU; the
+`-m gpu` tests pin the kernels themselves."""
+import numpy as np
+import pytest
+
+import helpers as H
+from gym_solo_b200 import _abi
+
+
+@pytest.fixture(scope='module')
+def world():
+  blob, model, config = H.model_and_config(dt=1 / 240.)
+  orc = H.oracle(model, config)
+  snap = orc.settle(H.START_TARGETS)
+  return model, config, orc, snap
+
+
+def test_float64_core_tracks_oracle_over_contact_rollout(world):
+  """Same algorithm, different formulation (whitened rows vs dense M^-1 J^T):
+  in double precision the two must agree to rounding over a contact-rich rollout."""
+  model, config, orc, snap = world
+  rng = np.random.RandomState(3)
+  a, b = snap.copy(), snap.copy()
+  worst_free, worst_step = 0.0, 0.0
+  its = []
+  for k in range(300):
+    act = rng.uniform(-2 * np.pi, 2 * np.pi, 12)
+    c, d = H.hostsim_step(model, config, a, act, use_double=True)    # same state in
+    b, _ = H.hostsim_step(model, config, b, act, use_double=True)    # free running
+    a = orc.step(a, act)
+    its.append(d['iterations'])
+    worst_step = max(worst_step, np.abs(a - c).max())
+    worst_free = max(worst_free, np.abs(a - b).max())
+  assert worst_step < 1e-10, worst_step
+  assert worst_free < 1e-5, worst_free
+  assert max(its) > 10          # the rollout exercises long PGS solves too
+
+
+def test_float32_core_single_step_within_north_star_tolerance(world):
+  """BASELINE.json north_star: <= 1e-4 rad and <= 1e-3 rad/s per step at dt = 1/240."""
+  model, config, orc, snap = world
+  rng = np.random.RandomState(4)
+  s = snap.copy()
+  worst = dict(q=0., qd=0., base_pos=0., base_rot=0., base_lin=0., base_ang=0.)
+  nf_err = 0.0
+  for k in range(200):
+    act = rng.uniform(-2 * np.pi, 2 * np.pi, 12)
+    s32 = s.astype(np.float32).astype(np.float64)
+    a32 = act.astype(np.float32).astype(np.float64)
+    want, wd = orc.step(s32, a32, diag=True)
+    got, d = H.hostsim_step(model, config, s32, a32, use_double=False)
+    e = H.state_errors(got, want, model.ndof)
+    for key in worst:
+      worst[key] = max(worst[key], e[key])
+    assert d['n_contacts'] == wd['n_contacts']
+    nf_err = max(nf_err, np.abs(d['normal_force'] - wd['normal_force'][:model.n_cand]).max())
+    s = want
+  assert worst['q'] <= 1e-4 and worst['qd'] <= 1e-3, worst
+  assert worst['base_pos'] <= 1e-5 and worst['base_rot'] <= 1e-4, worst
+  assert worst['base_lin'] <= 1e-3 and worst['base_ang'] <= 2e-3, worst
+  assert nf_err <= 0.5, nf_err      # N, contact normal force per support point
+
+
+def test_torque_mode_and_free_flight(world):
+  model, _, _, snap = world
+  _, _, cfg = H.model_and_config(dt=1 / 240., control_mode=1)
+  orc = H.oracle(model, cfg)
+  s = snap.copy()
+  s[2] += 0.5          # airborne: no contacts, no motor rows -> zero PGS iterations
+  act = np.zeros(12)
+  act[[0, 1, 3, 4]] = [0.5, -0.3, 1.0, 2.5]     # 2.5 > limit 2 -> clamped
+  for _ in range(20):
+    want = orc.step(s, act)
+    got, d = H.hostsim_step(model, cfg, s, act, use_double=True)
+    assert d['n_contacts'] == 0 and d['iterations'] == 0
+    np.testing.assert_allclose(got, want, atol=1e-10)
+    s = want
