@@ -243,6 +243,17 @@ def main():
   per_step_ms = np.array([s.elapsed_time(e) for s, e in zip(starts, ends)])
   total_ms = float(per_step_ms.sum())
 
+  # ---- per-kernel durations, live (CUDA events on the launching stream inside the C-ABI) --
+  env.client.phase_timing(True)
+  for k in range(min(args.steps, 200)):
+    a = fresh_actions()
+    if flush is not None:
+      flush.fill_(k & 0xff)
+    env.step(a)
+  phase_steps, phase_ms = env.client.phase_times()
+  env.client.phase_timing(False)
+  phase_ms = [m / max(1, phase_steps) for m in phase_ms]
+
   # ---- end-to-end arm: host buffers through solo_step_host -----------------------------
   rng = np.random.RandomState(4321 + rank)
   host_actions = [rng.uniform(-two_pi, two_pi, (n, 12)).astype(np.float32) for _ in range(16)]
@@ -277,7 +288,10 @@ def main():
     value = world * n * args.steps / (total_ms * 1e-3)
     e2e_value = world * n * e2e_steps / (max(e2e_ms, e2e_wall_ms) * 1e-3)
     peak, peak_kind = hbm_peak()
-    launch_ms = float(per_step_ms.mean())
+    step_ms = float(per_step_ms.mean())
+    names = ['setup_kernel', 'solve_kernel', 'finish_kernel']
+    dom = int(np.argmax(phase_ms))
+    launch_ms = phase_ms[dom]
     achieved = BYTES_PER_ENV_STEP * n / (launch_ms * 1e-3) / 1e9
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
@@ -291,9 +305,12 @@ def main():
                    'timing': 'CUDA events around every step on the launching stream, summed; max over ranks'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': None, 'peak_source': peak_kind,
-                     'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': 'setup_kernel<2> + solve_kernel<2,false> + finish_kernel<2> (one env.step)',
-                     'launch_ms_mean': launch_ms, 'launch_ms_p50': float(np.median(per_step_ms)),
-                     'launch_ms_max': float(per_step_ms.max()),
+                     'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': names[dom],
+                     'launch_ms_mean': launch_ms,
+                     'kernels_ms_mean': dict(zip(names, phase_ms)), 'kernel_share_of_step': launch_ms / sum(phase_ms),
+                     'step_ms_mean': step_ms, 'step_ms_p50': float(np.median(per_step_ms)),
+                     'step_ms_max': float(per_step_ms.max()),
+                     'whole_step_frac': BYTES_PER_ENV_STEP * n / (step_ms * 1e-3) / 1e9 / peak,
                      'note': 'path is FP32-issue/latency bound, not HBM bound (SURVEY.md 8d)'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * n * 12 * 4,
                 'd2h_bytes_per_step': world * n * (21 * 4 + 4 + 1), 'steps': e2e_steps,
