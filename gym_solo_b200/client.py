@@ -226,6 +226,14 @@ class BatchedClient:
       raise _lib.SoloError('solo_phase_times failed')
     return n, [float(ms[0]), float(ms[1]), float(ms[2])]
 
+  def solver_stats(self):
+    """[4, N] float32 copy: PGS iterations, contacts, contacts that carried an
+    impulse, SM cycles of the last physics step's solve, per environment."""
+    ptr = C.c_void_p()
+    _lib.check(self.lib.solo_solver_stats(self.handle, C.byref(ptr)), self.handle)
+    off = (ptr.value - self.scratch.data_ptr())
+    return self.scratch[off:off + 16 * self.n].view(torch.float32).view(4, self.n).clone()
+
   def solver_lanes(self):
     return int(self.lib.solo_solver_lanes(self.handle))
 

@@ -11,6 +11,7 @@
 #include "../../include/solo8_b200.h"
 #include "solo_convert.h"
 #include "solo_kernels.cuh"
+#include "solo_solve_warp.cuh"
 
 using namespace solo;
 
@@ -22,7 +23,8 @@ struct SoloHandle_ {
   int state_dim;
   int obs_dim;
   int block;              // threads per block of the one-thread-per-env kernels
-  int lanes;              // environments per warp in the solver kernel
+  int lanes;              // environments per warp in the lane-per-env solver kernel
+  bool warp_solver;       // one warp per environment (default) or one lane per environment
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
   bool bound;
@@ -104,7 +106,7 @@ static ScratchLayout scratch_layout(const SoloHandle h) {
   size_t off = 0;
   L.cand = off; off = align256(off + sizeof(float) * 4 * kMaxCand);
   L.hdr = off;  off = align256(off + sizeof(uint32_t) * 2 * n);
-  L.yh = off;   off = align256(off + sizeof(float) * (6 + kLegs * h->ch) * n);
+  L.yh = off;   off = align256(off + sizeof(float) * (6 + kLegs * h->ch + 4) * n);
   L.fac = off;  off = align256(off + sizeof(float) * facs * n);
   L.rows = off; off = align256(off + sizeof(float) * slots * n * row);
   L.total = off;
@@ -154,6 +156,10 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->obs_dim = 0;
   h->block = pick_block(n_envs);
   h->lanes = pick_lanes(n_envs);
+  {
+    const char *e = getenv("SOLO_SOLVER");
+    h->warp_solver = !(e && strcmp(e, "lane") == 0);
+  }
   h->motor_mask = 0;
   if (config->control_mode == SOLO_CONTROL_POSITION)
     for (int l = 0; l < model->n_legs; l++)
@@ -317,8 +323,13 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
-    if (dbg) solve_kernel<2, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-    else solve_kernel<2, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    if (h->warp_solver) {
+      if (dbg) solve_warp_kernel<2, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
+      else solve_warp_kernel<2, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
+    } else {
+      if (dbg) solve_kernel<2, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+      else solve_kernel<2, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    }
     if ((rc = check_launch(h, "solve_kernel"))) return rc;
     SOLO_MARK(2);
     finish_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
@@ -326,8 +337,13 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
-    if (dbg) solve_kernel<3, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-    else solve_kernel<3, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    if (h->warp_solver) {
+      if (dbg) solve_warp_kernel<3, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
+      else solve_warp_kernel<3, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
+    } else {
+      if (dbg) solve_kernel<3, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+      else solve_kernel<3, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
+    }
     if ((rc = check_launch(h, "solve_kernel"))) return rc;
     SOLO_MARK(2);
     finish_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
@@ -447,6 +463,13 @@ int64_t solo_phase_times(SoloHandle h, double *ms3) {
 
 int solo_block_size(SoloHandle h) { return h ? h->block : SOLO_EINVAL; }
 
-int solo_solver_lanes(SoloHandle h) { return h ? h->lanes : SOLO_EINVAL; }
+int solo_solver_stats(SoloHandle h, const float **stats_dev) {
+  if (!h || !stats_dev) return SOLO_EINVAL;
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  *stats_dev = h->B.yh + (size_t)(6 + kLegs * h->ch) * (size_t)h->B.n;
+  return SOLO_OK;
+}
+
+int solo_solver_lanes(SoloHandle h) { return h ? (h->warp_solver ? 0 : h->lanes) : SOLO_EINVAL; }
 
 }  // extern "C"

@@ -53,7 +53,7 @@ struct Buffers {
   // solver scratch (caller-bound, solo_scratch_bytes)
   const float *cand_tab;     // [n_cand][4] support point xyz + friction
   uint32_t *hdr;             // [2][n] contact-group ends, contact count
-  float *yh;                 // [6 + kLegs * CH][n]
+  float *yh;                 // [6 + kLegs * CH + 4][n]: solver output, then per-env solver statistics
   float *fac;                // [FactorLayout<CH>::kSize][n]
   float *rows;               // [n][RowLayout<CH>::kSlots][kRow]: one contiguous record list per env
   int32_t n;
@@ -180,7 +180,16 @@ solve_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const ui
     float yb[6], yl[kLegs][CH], mlam[kLegs * CH];
     const float *rows = B.rows + env * (RL::kSlots * RL::kRow);
     const int64_t slot_stride = RL::kRow;
-    iters = solve_rows<float, CH>(C, motor_mask, rows, slot_stride, h, lam_sm + lane, lanes, yb, yl, mlam);
+    const long long t0 = clock64();
+    int n_active = 0;
+    iters = solve_rows<float, CH>(C, motor_mask, rows, slot_stride, h, lam_sm + lane, lanes, yb, yl, mlam, &n_active);
+    {
+      // per-env solver statistics (rows kYh.. of the yh block): iterations, contacts,
+      // contacts that carried an impulse, SM cycles spent in the solve
+      float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
+      st[0] = (float)iters; st[(int64_t)B.n] = (float)h.nc; st[2 * (int64_t)B.n] = (float)n_active;
+      st[3 * (int64_t)B.n] = (float)(clock64() - t0);
+    }
     contacts = (int)h.nc;
     float *y = B.yh + env;
 #pragma unroll
@@ -213,7 +222,7 @@ solve_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const ui
       }
     }
   }
-  if (B.diag) diag_add(B.diag, contacts, iters, 0, live ? 1 : 0);
+  (void)contacts; (void)iters;   // solver statistics are folded into B.diag by finish_kernel
 }
 
 // ---------------------------------------------------------------------------------
@@ -251,9 +260,13 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
     finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
     if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
   }
+  if (B.diag) {
+    // fold this step's per-env solver statistics into the running totals
+    const float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
+    diag_add(B.diag, live ? (int)st[(int64_t)B.n] : 0, live ? (int)st[0] : 0, nan, live ? 1 : 0);
+  }
   if (!epilogue) {
     if (live) store_state<float, CH, float>(M, s, B.state + env, B.n);
-    if (B.diag && nan) atomicAdd(B.diag + 2, 1ull);
     return;
   }
 
@@ -302,7 +315,6 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
     for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
   }
   tile_scatter(obs_out, env0, n_valid, od, smem);
-  if (B.diag && nan) atomicAdd(B.diag + 2, 1ull);
 }
 
 // obs_factory.get_obs() / reward_factory.get_reward() on the current state

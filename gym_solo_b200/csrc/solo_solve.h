@@ -23,7 +23,7 @@ namespace solo {
 template <typename T, int CH>
 SOLO_HD int solve_rows(const ConfigT<T> &C, const uint32_t motor_mask, const T *rows, const int64_t slot_stride,
                        const RowHeader h, T *lam, const int64_t lam_stride, T (&yb)[6], T (&yl)[kLegs][CH],
-                       T (&mlam)[kLegs * CH]) {
+                       T (&mlam)[kLegs * CH], int *n_active = nullptr) {
   typedef RowLayout<CH> RL;
   const int nc = (int)h.nc;
   const int ends[kLegs + 1] = {(int)(h.ends03 & 255u), (int)((h.ends03 >> 8) & 255u), (int)((h.ends03 >> 16) & 255u),
@@ -190,6 +190,11 @@ SOLO_HD int solve_rows(const ConfigT<T> &C, const uint32_t motor_mask, const T *
     }
     it++;
     if (res <= C.res_thr) break;
+  }
+  if (n_active) {
+    int k = 0;
+    for (uint64_t m = active; m != 0; m &= m - 1) k++;
+    *n_active = k;
   }
   return it;
 }

@@ -216,7 +216,13 @@ int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
 int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev);
 /* Threads per block of the one-thread-per-environment kernels (setup, finish). */
 int solo_block_size(SoloHandle h);
-/* Environments per warp in the solver kernel (SOLO_LANES overrides). */
+/* Per-environment solver statistics of the last physics step, float[4][n_envs]
+ * inside the bound scratch: PGS iterations, contact points, contact points that
+ * carried an impulse, SM cycles spent in the solve. */
+int solo_solver_stats(SoloHandle h, const float **stats_dev);
+/* 0: the solver runs one warp per environment (default); otherwise the
+ * environments per warp of the lane-per-environment solver (SOLO_SOLVER=lane,
+ * SOLO_LANES). */
 int solo_solver_lanes(SoloHandle h);
 /* Live per-kernel timing (bench.py roofline): while enabled every physics step
  * records CUDA events on the launching stream around its three kernels;

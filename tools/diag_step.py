@@ -44,4 +44,9 @@ for k in range(100):
   env.step(acts[k % 64])
 cnt, ms = env.client.phase_times()
 out['phase_ms_flushed'] = [m / cnt for m in ms]
+st = env.client.solver_stats().cpu().numpy()
+order = np.argsort(-st[3])[:8]
+out['worst_envs_iters_nc_active_cycles'] = [[int(st[0, i]), int(st[1, i]), int(st[2, i]), int(st[3, i])] for i in order]
+out['mean_iters_nc_active_cycles'] = [float(st[k].mean()) for k in range(4)]
+out['max_nc'] = int(st[1].max())
 print(json.dumps(out))
