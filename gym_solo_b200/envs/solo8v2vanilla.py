@@ -247,7 +247,5 @@ class Solo8VanillaEnv(Solo8BaseEnv):
                         self.client.diag[2].to(torch.float32)])
     if not all_gather:
       return mine
-    import torch.distributed as dist
-    out = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
-    dist.all_gather(out, mine)
-    return torch.stack(out)
+    from gym_solo_b200 import sharding
+    return sharding.gather_statistics(mine)
