@@ -23,8 +23,6 @@ struct SoloHandle_ {
   int state_dim;
   int obs_dim;
   int block;              // threads per block of the one-thread-per-env kernels
-  int lanes;              // environments per warp in the lane-per-env solver kernel
-  bool warp_solver;       // one warp per environment (default) or one lane per environment
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
   bool bound;
@@ -78,37 +76,21 @@ static int pick_block(int n_envs) {
   return 128;
 }
 
-// Solver kernel: environments per warp.  A small batch is spread thin so that
-// every SM sub-partition (148 x 4) gets a warp and a warp waits only for the
-// slowest of `lanes` serial chains; large batches fill the warps.
-static int pick_lanes(int n_envs) {
-  const char *e = getenv("SOLO_LANES");
-  if (e) {
-    int l = atoi(e);
-    if (l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32) return l;
-  }
-  int l = 32;
-  while (l > 8 && (n_envs + l - 1) / l < 148 * 4) l >>= 1;
-  return l;
-}
-
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct ScratchLayout {
-  size_t cand, hdr, yh, fac, rows, total;
+  size_t cand, yh, fac, kin, total;
 };
 static ScratchLayout scratch_layout(const SoloHandle h) {
   const size_t n = (size_t)h->B.n;
-  const size_t row = h->ch == 2 ? RowLayout<2>::kRow : RowLayout<3>::kRow;
-  const size_t slots = h->ch == 2 ? RowLayout<2>::kSlots : RowLayout<3>::kSlots;
   const size_t facs = h->ch == 2 ? FactorLayout<2>::kSize : FactorLayout<3>::kSize;
+  const size_t kins = h->ch == 2 ? KinLayout<2>::kSize : KinLayout<3>::kSize;
   ScratchLayout L;
   size_t off = 0;
-  L.cand = off; off = align256(off + sizeof(float) * 4 * kMaxCand);
-  L.hdr = off;  off = align256(off + sizeof(uint32_t) * 2 * n);
+  L.cand = off; off = align256(off + sizeof(float) * kCandStride * kMaxCand);
   L.yh = off;   off = align256(off + sizeof(float) * (6 + kLegs * h->ch + 4) * n);
   L.fac = off;  off = align256(off + sizeof(float) * facs * n);
-  L.rows = off; off = align256(off + sizeof(float) * slots * n * row);
+  L.kin = off;  off = align256(off + sizeof(float) * kins * n);
   L.total = off;
   return L;
 }
@@ -155,11 +137,6 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->state_dim = SOLO_STATE_DIM(model->ndof);
   h->obs_dim = 0;
   h->block = pick_block(n_envs);
-  h->lanes = pick_lanes(n_envs);
-  {
-    const char *e = getenv("SOLO_SOLVER");
-    h->warp_solver = !(e && strcmp(e, "lane") == 0);
-  }
   h->motor_mask = 0;
   if (config->control_mode == SOLO_CONTROL_POSITION)
     for (int l = 0; l < model->n_legs; l++)
@@ -222,7 +199,7 @@ int solo_obs_dim(SoloHandle h) { return h ? h->obs_dim : SOLO_EINVAL; }
 
 int64_t solo_scratch_bytes(SoloHandle h) {
   if (!h) return SOLO_EINVAL;
-  return (int64_t)scratch_layout(h).total;   // rows, factors, yh, headers, support-point table
+  return (int64_t)scratch_layout(h).total;   // per-env records, factors, yh, support-point table
 }
 
 int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snapshot_dev, float *stats_dev,
@@ -233,15 +210,23 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
     const ScratchLayout L = scratch_layout(h);
     char *base = (char *)scratch_dev;
     h->B.cand_tab = (const float *)(base + L.cand);
-    h->B.hdr = (uint32_t *)(base + L.hdr);
     h->B.yh = (float *)(base + L.yh);
     h->B.fac = (float *)(base + L.fac);
-    h->B.rows = (float *)(base + L.rows);
-    float tab[4 * kMaxCand];
+    h->B.kin = (float *)(base + L.kin);
+    // support-point table of the solver warp: xyz, friction, leg (-1 base), depth in the chain
+    static float tab[kCandStride * kMaxCand];
     memset(tab, 0, sizeof tab);
-    for (int c = 0; c < h->K.M.n_cand; c++) {
-      for (int k = 0; k < 3; k++) tab[4 * c + k] = h->K.M.cand_pos[c][k];
-      tab[4 * c + 3] = h->K.M.cand_mu[c];
+    const ModelT<float> &M = h->K.M;
+    for (int body = 0; body <= M.ndof; body++) {
+      int leg = -1, depth = 0;
+      for (int l = 0; l < M.n_legs; l++)
+        if (body >= 1 && body - 1 >= M.dof0[l] && body - 1 < M.dof0[l] + M.chain_len[l]) { leg = l; depth = body - 1 - M.dof0[l]; }
+      for (int c = M.cand_begin[body]; c < M.cand_begin[body + 1]; c++) {
+        for (int k = 0; k < 3; k++) tab[kCandStride * c + k] = M.cand_pos[c][k];
+        tab[kCandStride * c + 3] = M.cand_mu[c];
+        tab[kCandStride * c + 4] = (float)leg;
+        tab[kCandStride * c + 5] = (float)depth;
+      }
     }
     DeviceGuard g(h->device);
     cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof tab, cudaMemcpyHostToDevice);
@@ -304,8 +289,7 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
                           cudaStream_t st) {
   const int grid = (h->B.n + h->block - 1) / h->block;
   const size_t sm = tile_smem(h);
-  const int sgrid = (h->B.n + h->lanes - 1) / h->lanes;
-  const size_t lam_sm = sizeof(float) * 3 * kMaxContacts * h->lanes;
+  const float margin = h->K.M.margin;
   const bool dbg = h->B.dbg_normal_force || h->B.dbg_motor_torque;
   const int ndof = h->K.M.ndof, n_cand = h->K.M.n_cand;
   int rc;
@@ -323,13 +307,8 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
-    if (h->warp_solver) {
-      if (dbg) solve_warp_kernel<2, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
-      else solve_warp_kernel<2, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
-    } else {
-      if (dbg) solve_kernel<2, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-      else solve_kernel<2, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-    }
+    if (dbg) solve_warp_kernel<2, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
+    else solve_warp_kernel<2, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
     if ((rc = check_launch(h, "solve_kernel"))) return rc;
     SOLO_MARK(2);
     finish_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
@@ -337,13 +316,8 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
-    if (h->warp_solver) {
-      if (dbg) solve_warp_kernel<3, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
-      else solve_warp_kernel<3, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand);
-    } else {
-      if (dbg) solve_kernel<3, true><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-      else solve_kernel<3, false><<<sgrid, 32, lam_sm, st>>>(h->K.C, h->B, h->motor_mask, h->lanes, ndof, n_cand);
-    }
+    if (dbg) solve_warp_kernel<3, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
+    else solve_warp_kernel<3, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
     if ((rc = check_launch(h, "solve_kernel"))) return rc;
     SOLO_MARK(2);
     finish_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
@@ -470,6 +444,6 @@ int solo_solver_stats(SoloHandle h, const float **stats_dev) {
   return SOLO_OK;
 }
 
-int solo_solver_lanes(SoloHandle h) { return h ? (h->warp_solver ? 0 : h->lanes) : SOLO_EINVAL; }
+int solo_solver_lanes(SoloHandle h) { return h ? 0 : SOLO_EINVAL; }   // one warp per environment
 
 }  // extern "C"

@@ -2,19 +2,16 @@
 //
 // One env.step = three launches on the caller's stream (solo_phases.h):
 //
-//   setup_kernel   one thread per environment.  Reads the action tile and the
-//                  SoA state, runs the articulated-body setup, writes the
-//                  constraint rows [env][slot][kRow] (48/64-byte records, one
-//                  contiguous list per environment so that the solver walks
-//                  consecutive cache lines), the mass-matrix
-//                  factors [k][env] and the per-env contact header.
-//   solve_kernel   the data-dependent part: projected Gauss-Seidel, a serial
-//                  chain of 8 + 3 n_contacts row updates x 2..50 iterations per
-//                  environment.  Environments are spread `lanes` per warp so
-//                  that a small batch still covers every SM sub-partition and a
-//                  warp only waits for the slowest of `lanes` environments.
-//                  Rows stream from L1/L2 one update ahead; impulses live in
-//                  shared memory; yh in registers.
+//   setup_kernel   one thread per environment: the part of a step whose size
+//                  does not depend on the pose.  Reads the action tile and the
+//                  SoA state, runs kinematics, bias forces, the mass-matrix
+//                  factorisation and the motor rows; writes the factors [k][env]
+//                  for finish_kernel and one contiguous KinLayout record per
+//                  environment for the solver warp.
+//   solve_warp_kernel (solo_solve_warp.cuh)  one warp per environment: contact
+//                  detection and contact rows one contact per lane, then the
+//                  data-dependent part: projected Gauss-Seidel, a serial chain
+//                  of 8 + 3 n_contacts row updates x 2..50 iterations.
 //   finish_kernel  one thread per environment: dv = T^T yh, integration, NaN
 //                  guard, observations, reward, termination, optional snapshot
 //                  auto-reset; writes the SoA state and the [env][k] outputs
@@ -51,11 +48,10 @@ struct Buffers {
   float *dbg_normal_force;   // [n_cand][n] or null
   float *dbg_motor_torque;   // [ndof][n] or null
   // solver scratch (caller-bound, solo_scratch_bytes)
-  const float *cand_tab;     // [n_cand][4] support point xyz + friction
-  uint32_t *hdr;             // [2][n] contact-group ends, contact count
+  const float *cand_tab;     // [kMaxCand][kCandStride] support point xyz, friction, leg, depth
   float *yh;                 // [6 + kLegs * CH + 4][n]: solver output, then per-env solver statistics
   float *fac;                // [FactorLayout<CH>::kSize][n]
-  float *rows;               // [n][RowLayout<CH>::kSlots][kRow]: one contiguous record list per env
+  float *kin;                // [n][KinLayout<CH>::kSize]: one contiguous record per env
   int32_t n;
   int32_t obs_dim;
 };
@@ -135,6 +131,7 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
              const int broadcast, const float action_scale) {
   extern __shared__ float smem[];
   typedef RowLayout<CH> RL;
+  typedef KinLayout<CH> KL;
   const ModelT<float> &M = K.M;
   const int64_t env0 = (int64_t)blockIdx.x * blockDim.x;
   const int64_t env = env0 + threadIdx.x;
@@ -153,76 +150,8 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
   if (!live) return;
   EnvState<float, CH> s;
   load_state<float, CH, float>(M, B.state + env, B.n, s);
-  const RowHeader h = setup_step<float, CH>(M, K.C, s, cmd, B.cand_tab, B.rows + env * (RL::kSlots * RL::kRow),
-                                            RL::kRow, B.fac + env, B.n);
-  B.hdr[env] = h.ends03;
-  B.hdr[(int64_t)B.n + env] = h.nc;
-}
-
-// ---------------------------------------------------------------------------------
-// phase 2: the constraint solver of stepSimulation.  One warp per block; lanes
-// [0, lanes) of warp w own environments w * lanes + lane.
-// ---------------------------------------------------------------------------------
-template <int CH, bool DBG>
-__global__ void __launch_bounds__(32)
-solve_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const uint32_t motor_mask, const int lanes,
-             const int ndof_total, const int n_cand) {
-  extern __shared__ float lam_sm[];   // [3 * kMaxContacts][lanes]
-  typedef RowLayout<CH> RL;
-  const int lane = threadIdx.x;
-  const int64_t env = (int64_t)blockIdx.x * lanes + lane;
-  const bool live = lane < lanes && env < B.n;
-  int contacts = 0, iters = 0;
-  if (live) {
-    RowHeader h;
-    h.ends03 = B.hdr[env];
-    h.nc = B.hdr[(int64_t)B.n + env];
-    float yb[6], yl[kLegs][CH], mlam[kLegs * CH];
-    const float *rows = B.rows + env * (RL::kSlots * RL::kRow);
-    const int64_t slot_stride = RL::kRow;
-    const long long t0 = clock64();
-    int n_active = 0;
-    iters = solve_rows<float, CH>(C, motor_mask, rows, slot_stride, h, lam_sm + lane, lanes, yb, yl, mlam, &n_active);
-    {
-      // per-env solver statistics (rows kYh.. of the yh block): iterations, contacts,
-      // contacts that carried an impulse, SM cycles spent in the solve
-      float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
-      st[0] = (float)iters; st[(int64_t)B.n] = (float)h.nc; st[2 * (int64_t)B.n] = (float)n_active;
-      st[3 * (int64_t)B.n] = (float)(clock64() - t0);
-    }
-    contacts = (int)h.nc;
-    float *y = B.yh + env;
-#pragma unroll
-    for (int a = 0; a < 6; a++) y[(int64_t)a * B.n] = yb[a];
-#pragma unroll
-    for (int l = 0; l < kLegs; l++)
-#pragma unroll
-      for (int k = 0; k < CH; k++) y[(int64_t)(6 + l * CH + k) * B.n] = yl[l][k];
-    if (DBG) {
-      if (B.dbg_normal_force) {
-        for (int c = 0; c < n_cand; c++) B.dbg_normal_force[(int64_t)c * B.n + env] = 0.f;
-        for (int i = 0; i < (int)h.nc; i++) {
-          const float *nr = rows + (int64_t)(RL::kMotorSlots + 3 * i) * slot_stride;
-          B.dbg_normal_force[(int64_t)(int)nr[RL::kX] * B.n + env] = lam_sm[(3 * i) * lanes + lane] * nr[RL::kIs] * C.inv_dt;
-        }
-      }
-      if (B.dbg_motor_torque) {
-        // dof order == (leg, joint) order with inactive slots skipped
-        int d = 0;
-        if (motor_mask == 0)
-          for (int k = 0; k < ndof_total; k++) B.dbg_motor_torque[(int64_t)k * B.n + env] = 0.f;
-#pragma unroll
-        for (int j = 0; j < kLegs * CH; j++) {
-          if ((motor_mask >> j) & 1u) {
-            const float *mr = rows + (int64_t)j * slot_stride;
-            if (d < ndof_total) B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * mr[RL::kIs] * C.inv_dt;
-            d++;
-          }
-        }
-      }
-    }
-  }
-  (void)contacts; (void)iters;   // solver statistics are folded into B.diag by finish_kernel
+  float *kin = B.kin + env * KL::kSize;
+  setup_step<float, CH, false>(M, K.C, s, cmd, nullptr, kin + KL::kMotor, RL::kRow, B.fac + env, B.n, kin);
 }
 
 // ---------------------------------------------------------------------------------

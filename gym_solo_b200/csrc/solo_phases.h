@@ -59,6 +59,26 @@ template <int CH> struct FactorLayout {
   static constexpr int kSize = kVl + kLegs * CH;
 };
 
+// What setup_step<.., CONTACTS = false> leaves per environment for the solver
+// warp (one contiguous record, floats): the motor rows, the base factor Ls,
+// the post-drift velocities, and per leg the factors and joint frames a contact
+// row is built from.
+template <int CH> struct KinLayout {
+  static constexpr int kMotor = 0;                                           // kMotorSlots x kRow
+  static constexpr int kLs = RowLayout<CH>::kMotorSlots * RowLayout<CH>::kRow;   // 21: lower triangle, row major
+  static constexpr int kVb = kLs + 21;                                       // 6
+  static constexpr int kC0 = kVb + 6;                                        // 3  base COM, world
+  static constexpr int kO0 = kC0 + 3;                                        // 3  base frame origin
+  static constexpr int kR0 = kO0 + 3;                                        // 9  base rotation
+  static constexpr int kLeg = kR0 + 9;
+  static constexpr int kE = 0;                                               // CH (CH + 1) / 2, lower, row major
+  static constexpr int kBh = CH * (CH + 1) / 2;                              // CH x 6
+  static constexpr int kVl = kBh + CH * 6;                                   // CH
+  static constexpr int kJoint = kVl + CH;                                    // per joint: axis 3, origin 3, rotation 9
+  static constexpr int kLegSize = kJoint + CH * 15;
+  static constexpr int kSize = (kLeg + kLegs * kLegSize + 3) & ~3;           // 328 (CH 2), 524 (CH 3)
+};
+
 // Per-env header: contact-group ends (base, leg 0..3), 8 bits each.
 struct RowHeader {
   uint32_t ends03;   // leg_end[0..3]

@@ -12,10 +12,15 @@ namespace solo {
 // lane-indexed copy of M.cand_pos / M.cand_mu: shared memory on the device).
 // rows: row r lives at rows[r * slot_stride + 0..kRow); fac: fac[k * fac_stride].
 // Returns the header (contact counts per group).
-template <typename T, int CH>
+//
+// CONTACTS = false (the CUDA path): stop after the motor rows and leave, in
+// `kin` (KinLayout<CH>, one contiguous record per environment, motor rows
+// included: pass rows = kin + KinLayout::kMotor), what the solver warp needs to
+// build the contact rows itself, one contact per lane (solo_contact.cuh).
+template <typename T, int CH, bool CONTACTS = true>
 SOLO_HD RowHeader setup_step(const ModelT<T> &M, const ConfigT<T> &C, const EnvState<T, CH> &s,
                              const T (&cmd)[kLegs][CH], const T *cand_tab, T *rows, int64_t slot_stride, T *fac,
-                             int64_t fac_stride) {
+                             int64_t fac_stride, T *kin = nullptr) {
   typedef RowLayout<CH> RL;
   typedef FactorLayout<CH> FL;
   const T dt = C.dt;
@@ -299,6 +304,47 @@ SOLO_HD RowHeader setup_step(const ModelT<T> &M, const ConfigT<T> &C, const EnvS
         store_row(dst, o);
       }
     }
+
+  if (!CONTACTS) {
+    typedef KinLayout<CH> KL;
+    int k = KL::kLs;
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) kin[k++] = S[i][j];
+#pragma unroll
+    for (int i = 0; i < 6; i++) kin[KL::kVb + i] = vb[i];
+    kin[KL::kC0] = c0.x; kin[KL::kC0 + 1] = c0.y; kin[KL::kC0 + 2] = c0.z;
+    kin[KL::kO0] = o0.x; kin[KL::kO0 + 1] = o0.y; kin[KL::kO0 + 2] = o0.z;
+#pragma unroll
+    for (int i = 0; i < 9; i++) kin[KL::kR0 + i] = R0.m[i];
+#pragma unroll
+    for (int l = 0; l < kLegs; l++) {
+      T *kl = kin + KL::kLeg + l * KL::kLegSize;
+      int e = KL::kE;
+#pragma unroll
+      for (int i = 0; i < CH; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) kl[e++] = E[l][i][j];
+#pragma unroll
+      for (int i = 0; i < CH; i++)
+#pragma unroll
+        for (int a = 0; a < 6; a++) kl[KL::kBh + i * 6 + a] = Bh[l][i][a];
+#pragma unroll
+      for (int i = 0; i < CH; i++) kl[KL::kVl + i] = vl[l][i];
+#pragma unroll
+      for (int j = 0; j < CH; j++) {
+        T *kj = kl + KL::kJoint + j * 15;
+        kj[0] = ja[l][j].x; kj[1] = ja[l][j].y; kj[2] = ja[l][j].z;
+        kj[3] = jo[l][j].x; kj[4] = jo[l][j].y; kj[5] = jo[l][j].z;
+#pragma unroll
+        for (int i = 0; i < 9; i++) kj[6 + i] = jR[l][j].m[i];
+      }
+    }
+    RowHeader h0;
+    h0.ends03 = 0; h0.nc = 0;
+    return h0;
+  }
 
   // ---------------- contact rows ----------------
   int nc = 0;

@@ -1,52 +1,65 @@
-// solo_solve_warp.cuh -- the constraint solver of stepSimulation with ONE WARP PER
-// ENVIRONMENT.  Same iterates as solo_solve.h (the sequential statement of the
-// algorithm, which tests/hostsim runs on the CPU), scheduled for LATENCY: the
-// launch lasts as long as its slowest environment (50 iterations x ~10 contacts
-// that carry an impulse), so what counts is the length of the dependent chain of
-// one Gauss-Seidel update.
+// solo_solve_warp.cuh -- contact detection, contact rows and the constraint solver
+// of stepSimulation with ONE WARP PER ENVIRONMENT.  Same iterates as solo_solve.h
+// (the sequential statement of the algorithm, which tests/hostsim runs on the
+// CPU), scheduled for LATENCY: a launch lasts as long as its slowest environment
+// (50 iterations x ~10 contacts that carry an impulse), and a warp running alone
+// issues one instruction every ~2 cycles, so what counts is the instruction count
+// and the dependent chain of one Gauss-Seidel update.
 //
-//   * the environment's row list is copied once from the L2-resident record list
-//     into shared memory (coalesced float4 copy); every later row access is a
-//     broadcast LDS whose address does not depend on yh, i.e. off the chain;
-//   * yh, all impulses and every piece of control flow are warp-uniform; impulses
-//     live in shared memory, written and read back by every lane (no __syncwarp);
-//   * lane l keeps the normal rows of contacts l and l + 32 as dense vectors in
-//     registers.  ~90 % of the rows inside Bullet's 2 cm breaking threshold are
-//     speculative (zero impulse, b' - u.yh <= 0: a no-op), so the normal phase
-//     walks the bitmask of contacts that HAVE carried an impulse with uniform
-//     updates (dot -> clamp -> axpy, ~50 cycles each) while the lanes check in
-//     parallel that no speculative row between two of them has come alive under
-//     the current yh; one that has is promoted on the spot, at its place in
-//     Bullet's order -- exactly sequential Gauss-Seidel;
-//   * the friction phase walks the same bitmask (only those contacts can hold
-//     friction: limit = mu * lambda_n), cone projection without a branch.
+//   * prologue: the environment's KinLayout record (written by setup_kernel) is
+//     copied to shared memory; the lanes test the model's support points against
+//     the ground plane, compact the hits by ballot (Bullet's order: by body, then
+//     by support point) and lane l builds the normal row of contact l (and l + 32)
+//     as a dense vector in registers -- no row ever goes through memory;
+//   * yh, all impulses and every piece of control flow are warp-uniform;
+//   * ~90 % of the rows inside Bullet's 2 cm breaking threshold are speculative
+//     (zero impulse, b' - u.yh <= 0: a no-op), so only the contacts that HAVE
+//     carried an impulse are updated, uniformly, while the lanes check in parallel
+//     that no speculative row between two of them has come alive under the
+//     current yh; one that has is promoted on the spot, at its place in Bullet's
+//     order -- exactly sequential Gauss-Seidel;
+//   * the promoted ("active") contacts live in shared memory as an array of dense
+//     records sorted by contact index: normal row, the friction pair, the three
+//     impulses, and the mask of speculative rows that precede the contact.  The
+//     walk over it is a counted loop: addresses are k * stride, nothing on the
+//     chain but the arithmetic.  A promotion (at most once per contact and solve)
+//     shifts the tail of the array; the owner lane builds the friction pair then;
+//   * friction: both rows on the same velocity, cone projection without a branch.
 #ifndef SOLO_SOLVE_WARP_CUH_
 #define SOLO_SOLVE_WARP_CUH_
 
+#include "solo_contact.cuh"
 #include "solo_kernels.cuh"
 
 namespace solo {
 
+// one active contact in shared memory (floats)
 template <int CH>
-struct WarpSolveSmem {
-  float row[RowLayout<CH>::kSlots][RowLayout<CH>::kRow];   // the env's row list (motor slots, then contacts)
-  float4 lam[kMaxContacts];                                // scaled impulses: normal, t1, t2, -
+struct ActiveLayout {
+  static constexpr int W = 6 + kLegs * CH;           // dense width
+  static constexpr int NW = (W + 2 + 3) & ~3;        // normal: u[W], b, s
+  static constexpr int FW = (W + 4 + 3) & ~3;        // friction: u[W], b, s, 1/s, mu/s_n
+  static constexpr int kFA = NW, kFB = NW + FW;
+  static constexpr int kMeta = NW + 2 * FW;          // lam_n, lam_a, lam_b, idx | range lo, range hi, cand, -
+  static constexpr int kSize = kMeta + 8;            // 64 floats (CH 2), 76 (CH 3)
 };
 
-// uniform: group (0 base, 1..4 legs) of contact c from the packed group ends
-__device__ __forceinline__ int contact_group(const uint32_t ends03, const int c) {
-  return (c >= (int)(ends03 & 255u)) + (c >= (int)((ends03 >> 8) & 255u)) + (c >= (int)((ends03 >> 16) & 255u)) +
-         (c >= (int)((ends03 >> 24) & 255u));
-}
+template <int CH>
+struct WarpSolveSmem {
+  float kin[KinLayout<CH>::kSize];                   // setup_kernel's record (motor rows first)
+  float ent[kMaxContacts][ActiveLayout<CH>::kSize];  // active contacts, sorted by contact index
+  int32_t list[kMaxContacts];                        // contact -> support point
+};
 
 // contact bitmasks: 32 bits when the env has <= 32 contacts (99.8 % of env-steps), else 64
 template <int NR> struct CMask;
 template <> struct CMask<1> {
   typedef uint32_t T;
   static __device__ __forceinline__ int first(T m) { return __ffs((int)m) - 1; }
+  static __device__ __forceinline__ int last(T m) { return 31 - __clz((int)m); }
   static __device__ __forceinline__ T bit(int c) { return 1u << c; }
   static __device__ __forceinline__ T below(int c) { return c >= 32 ? ~0u : ((1u << c) - 1u); }
-  static __device__ __forceinline__ int count(T m) { return __popc(m); }
+  static __device__ __forceinline__ T make(uint32_t lo, uint32_t) { return lo; }
 };
 template <> struct CMask<2> {
   typedef uint64_t T;
@@ -54,9 +67,10 @@ template <> struct CMask<2> {
     const uint32_t lo = (uint32_t)m;
     return lo ? __ffs((int)lo) - 1 : 31 + __ffs((int)(uint32_t)(m >> 32));
   }
+  static __device__ __forceinline__ int last(T m) { return 63 - __clzll((long long)m); }
   static __device__ __forceinline__ T bit(int c) { return 1ull << c; }
   static __device__ __forceinline__ T below(int c) { return c >= 64 ? ~0ull : ((1ull << c) - 1ull); }
-  static __device__ __forceinline__ int count(T m) { return __popcll(m); }
+  static __device__ __forceinline__ T make(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
 };
 
 __device__ __forceinline__ float fast_rsqrt(const float x) {
@@ -65,123 +79,86 @@ __device__ __forceinline__ float fast_rsqrt(const float x) {
   return r;
 }
 
-// A stored row as fetched from shared memory (broadcast LDS): the record, the
-// contact's impulses and its group.  Nothing here depends on yh, so a fetch can
-// be issued one update ahead.
+// compact row of a contact on leg `leg` (-1: base) -> dense u[W] followed by n_tail scalars
 template <int CH>
-struct CompactRow {
-  float r[RowLayout<CH>::kRow];
-  float4 lam;
-  int g;
-  __device__ __forceinline__ void fetch(const float *crow, const float4 *lams, const int c, const int k,
-                                        const uint32_t ends03) {
-    load_row(crow + (3 * c + k) * RowLayout<CH>::kRow, r);
-    lam = lams[c];
-    g = contact_group(ends03, c);
-  }
-};
-
-template <int G> struct IntC { static constexpr int value = G; };
-
-// (b + extra) - u . y for a compact row of group G (0 base, 1..4 leg G - 1): the
-// leg entries of y it touches are static
-template <int CH, int G>
-__device__ __forceinline__ float row_gap(const float (&r)[RowLayout<CH>::kRow], const float (&y)[6 + kLegs * CH],
-                                         const float extra) {
-  float a0 = r[RowLayout<CH>::kB] + extra, a1 = 0.f;
+__device__ __forceinline__ void store_dense(float *dst, const float (&row)[RowLayout<CH>::kRow], const int leg,
+                                            const int n_tail, const int width) {
+  typedef RowLayout<CH> RL;
+  constexpr int W = 6 + kLegs * CH;
 #pragma unroll
-  for (int a = 0; a < 6; a += 2) { a0 = fmaf(-r[a], y[a], a0); a1 = fmaf(-r[a + 1], y[a + 1], a1); }
-  if (G > 0) {
+  for (int a = 0; a < 6; a++) dst[a] = row[a];
 #pragma unroll
-    for (int k = 0; k < CH; k++) {
-      if (k & 1) a1 = fmaf(-r[6 + k], y[6 + (G > 0 ? G - 1 : 0) * CH + k], a1);
-      else a0 = fmaf(-r[6 + k], y[6 + (G > 0 ? G - 1 : 0) * CH + k], a0);
-    }
-  }
-  return a0 + a1;
-}
-// y += u * d for a compact row of group G
-template <int CH, int G>
-__device__ __forceinline__ void row_axpy(const float (&r)[RowLayout<CH>::kRow], const float d,
-                                         float (&y)[6 + kLegs * CH]) {
+  for (int l = 0; l < kLegs; l++)
 #pragma unroll
-  for (int a = 0; a < 6; a++) y[a] = fmaf(r[a], d, y[a]);
-  if (G > 0) {
+    for (int k = 0; k < CH; k++) dst[6 + l * CH + k] = (leg == l) ? row[6 + k] : 0.f;
 #pragma unroll
-    for (int k = 0; k < CH; k++) y[6 + (G > 0 ? G - 1 : 0) * CH + k] = fmaf(r[6 + k], d, y[6 + (G > 0 ? G - 1 : 0) * CH + k]);
-  }
+  for (int t = 0; t < 4; t++)
+    if (W + t < width) dst[W + t] = t < n_tail ? row[RL::kJ + t] : 0.f;
+  for (int a = W + 4; a < width; a++) dst[a] = 0.f;
 }
 
-// A compact row (6 base + CH own-leg entries) expanded to the dense width with
-// selects on the (uniform) group: the selects depend on the row and the group
-// only, so they run ahead of the yh chain.
+// b - u . y over a dense record (u at r[0..W), b at r[W]) in four accumulator chains
+template <int W, int N>
+__device__ __forceinline__ float dense_gap(const float (&r)[N], const float (&y)[W], const float extra) {
+  float a0 = r[W] + extra, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+  for (int a = 0; a < W; a++) {
+    if ((a & 3) == 0) a0 = fmaf(-r[a], y[a], a0);
+    else if ((a & 3) == 1) a1 = fmaf(-r[a], y[a], a1);
+    else if ((a & 3) == 2) a2 = fmaf(-r[a], y[a], a2);
+    else a3 = fmaf(-r[a], y[a], a3);
+  }
+  return (a0 + a1) + (a2 + a3);
+}
+
+// The owner lane of a promoted contact expands its three rows into entry `e`.
 template <int CH>
-struct DenseRow {
-  static constexpr int W = 6 + kLegs * CH;
-  float u[W];
-  float b, s, is, x;
-  __device__ __forceinline__ void load(const float *p, const int g) {
-    typedef RowLayout<CH> RL;
-    float r[RL::kRow];
-    load_row(p, r);
-#pragma unroll
-    for (int a = 0; a < 6; a++) u[a] = r[a];
-#pragma unroll
-    for (int l = 0; l < kLegs; l++)
-#pragma unroll
-      for (int k = 0; k < CH; k++) u[6 + l * CH + k] = (g == l + 1) ? r[6 + k] : 0.f;
-    b = r[RL::kB]; s = r[RL::kS]; is = r[RL::kIs]; x = r[RL::kX];
-  }
-  __device__ __forceinline__ void expand(const CompactRow<CH> &c) {
-    typedef RowLayout<CH> RL;
-#pragma unroll
-    for (int a = 0; a < 6; a++) u[a] = c.r[a];
-#pragma unroll
-    for (int l = 0; l < kLegs; l++)
-#pragma unroll
-      for (int k = 0; k < CH; k++) u[6 + l * CH + k] = (c.g == l + 1) ? c.r[6 + k] : 0.f;
-    b = c.r[RL::kB]; s = c.r[RL::kS]; is = c.r[RL::kIs]; x = c.r[RL::kX];
-  }
-  // (b + extra) - u . y in four accumulator chains
-  __device__ __forceinline__ float gap(const float (&y)[W], const float extra = 0.f) const {
-    float a0 = b + extra, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-    for (int a = 0; a < W; a++) {
-      if ((a & 3) == 0) a0 = fmaf(-u[a], y[a], a0);
-      else if ((a & 3) == 1) a1 = fmaf(-u[a], y[a], a1);
-      else if ((a & 3) == 2) a2 = fmaf(-u[a], y[a], a2);
-      else a3 = fmaf(-u[a], y[a], a3);
-    }
-    return (a0 + a1) + (a2 + a3);
-  }
-};
+__device__ __noinline__ void build_entry(float *e, const float *kin, const ConfigT<float> &C, const float margin,
+                                         const float *cand_tab, const int cand, const int contact, const float lam_n) {
+  typedef RowLayout<CH> RL;
+  typedef ActiveLayout<CH> AL;
+  const Cand k = load_cand(cand_tab, cand);
+  float rows[3][RL::kRow];
+  build_contact_rows<CH, 3>(kin, C, margin, k, cand, rows);
+  store_dense<CH>(e, rows[0], k.leg, 2, AL::NW);
+  store_dense<CH>(e + AL::kFA, rows[1], k.leg, 4, AL::FW);
+  store_dense<CH>(e + AL::kFB, rows[2], k.leg, 4, AL::FW);
+  e[AL::kMeta] = lam_n; e[AL::kMeta + 1] = 0.f; e[AL::kMeta + 2] = 0.f; e[AL::kMeta + 3] = __int_as_float(contact);
+  e[AL::kMeta + 4] = 0.f; e[AL::kMeta + 5] = 0.f; e[AL::kMeta + 6] = __int_as_float(cand); e[AL::kMeta + 7] = 0.f;
+}
 
 // The solve proper.  NR = dense normal rows per lane (1: <= 32 contacts, 2: <= 64).
-// Returns iterations; y = yh, mlam = scaled motor impulses, *n_active = contacts
-// that carried an impulse.
+// Returns iterations; y = yh, mlam = scaled motor impulses, *n_active = entries of sm.ent.
 template <int CH, int NR>
-__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH> &sm, const uint32_t motor_mask,
-                                          const uint32_t ends03, const int nc, const int lane,
-                                          float (&y)[6 + kLegs * CH], float (&mlam)[kLegs * CH], int *n_active) {
+__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH> &sm, const float margin,
+                                          const float *cand_tab, const uint32_t motor_mask, const int nc,
+                                          const int lane, float (&y)[6 + kLegs * CH], float (&mlam)[kLegs * CH],
+                                          int *n_active) {
   typedef RowLayout<CH> RL;
+  typedef KinLayout<CH> KL;
+  typedef ActiveLayout<CH> AL;
   typedef CMask<NR> MK;
   typedef typename MK::T mask_t;
-  constexpr int W = 6 + kLegs * CH;
+  constexpr int W = AL::W;
   constexpr unsigned FULL = 0xffffffffu;
-  const float *crow = &sm.row[RL::kMotorSlots][0];
 
   // this lane's normal rows, dense, for the whole solve
   float ud[NR][W], ub[NR];
-  bool valid[NR];
 #pragma unroll
   for (int r = 0; r < NR; r++) {
     const int c = lane + 32 * r;
-    valid[r] = c < nc;
-    DenseRow<CH> d;
-    d.load(crow + (3 * (valid[r] ? c : 0)) * RL::kRow, contact_group(ends03, c));
+    const bool valid = c < nc;
+    const int cand = valid ? sm.list[c] : 0;
+    const Cand k = load_cand(cand_tab, cand);
+    float row[1][RL::kRow];
+    build_contact_rows<CH, 1>(sm.kin, C, margin, k, cand, row);
 #pragma unroll
-    for (int a = 0; a < W; a++) ud[r][a] = valid[r] ? d.u[a] : 0.f;
-    ub[r] = valid[r] ? d.b : -1.f;   // an absent row never comes alive
+    for (int a = 0; a < 6; a++) ud[r][a] = valid ? row[0][a] : 0.f;
+#pragma unroll
+    for (int l = 0; l < kLegs; l++)
+#pragma unroll
+      for (int j = 0; j < CH; j++) ud[r][6 + l * CH + j] = (valid && k.leg == l) ? row[0][6 + j] : 0.f;
+    ub[r] = valid ? row[0][RL::kB] : -1.f;   // an absent row never comes alive
   }
 #pragma unroll
   for (int a = 0; a < W; a++) y[a] = 0.f;
@@ -189,7 +166,10 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   for (int j = 0; j < kLegs * CH; j++) mlam[j] = 0.f;
 
   const float mlim = C.torque_limit * C.dt;
-  mask_t act = 0;   // contacts that have carried a normal impulse
+  const mask_t all = MK::below(nc);
+  mask_t act = 0;          // contacts that have carried a normal impulse (= the entries of sm.ent)
+  mask_t tail_range = all; // speculative rows behind the last active contact
+  int n_act = 0;
   int it = 0;
   for (; it < C.iters;) {
     float res = 0.f;
@@ -199,7 +179,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         // dead slots (shorter chains) hold all-zero rows: no test needed
         const int j = l * CH + i;
         float r[RL::kRow];
-        load_row(&sm.row[j][0], r);
+        load_row(sm.kin + KL::kMotor + j * RL::kRow, r);
         float a0 = r[RL::kB], a1 = 0.f;
 #pragma unroll
         for (int a = 0; a < 6; a += 2) { a0 = fmaf(-r[a], y[a], a0); a1 = fmaf(-r[a + 1], y[a + 1], a1); }
@@ -231,151 +211,165 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
 
     if (nc > 0) {
       // ---- normal rows ----
-      // Walk `act` in contact order with uniform updates.  Before the update of
-      // the next active row every lane tests its own speculative rows that sit
-      // between the last processed row and that one against the current yh; the
-      // first that has come alive (b' - u.yh > 0 with a zero impulse) is promoted:
-      // it is applied now, at its place in the order, and joins `act`.
-      // Contacts are sorted by group (base, leg 0..3), so the walk is unrolled over
-      // the group: inside a group the leg a compact row touches is static.
-      const mask_t all = MK::below(nc);
-      int lo = 0;
-      auto normal_group = [&](auto gtag) {
-        constexpr int G = decltype(gtag)::value;
-        const int end = G < kLegs ? (int)((ends03 >> (8 * G)) & 255u) : nc;
-        mask_t rem = act & MK::below(end) & ~MK::below(lo);
-        for (;;) {
-          const int nxt = rem != 0 ? MK::first(rem) : end;
-          if (G < kLegs && nxt >= end) break;   // the pending range is screened by the next group
-          const mask_t range = MK::below(nxt) & ~MK::below(lo) & ~act & all;   // speculative rows in [lo, nxt)
-          if (range != 0) {
-            mask_t viol = 0;
-            float t[NR];
+      // Entry k of sm.ent is the k-th active contact; its `range` is the set of
+      // speculative rows between the previous active contact and itself.  Before
+      // entry k is updated those rows are screened against the current yh; the
+      // first that has come alive is promoted into slot k and applied.
+      for (int k = 0;;) {
+        const bool at_end = k >= n_act;
+        const float *e = &sm.ent[at_end ? 0 : k][0];
+        float nr[AL::NW];
+        load_row(e, nr);
+        const float4 m0 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
+        const float4 m1 = *reinterpret_cast<const float4 *>(e + AL::kMeta + 4);
+        const mask_t range = at_end ? tail_range : MK::make(__float_as_uint(m1.x), __float_as_uint(m1.y));
+        if (range != 0) {
+          mask_t viol = 0;
+          float t[NR];
 #pragma unroll
-            for (int q = 0; q < NR; q++) {
-              float a0 = ub[q], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+          for (int q = 0; q < NR; q++) {
+            float a0 = ub[q], a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-              for (int a = 0; a < W; a++) {
-                if ((a & 3) == 0) a0 = fmaf(-ud[q][a], y[a], a0);
-                else if ((a & 3) == 1) a1 = fmaf(-ud[q][a], y[a], a1);
-                else if ((a & 3) == 2) a2 = fmaf(-ud[q][a], y[a], a2);
-                else a3 = fmaf(-ud[q][a], y[a], a3);
-              }
-              t[q] = (a0 + a1) + (a2 + a3);
-              viol |= (mask_t)__ballot_sync(FULL, t[q] > 0.f) << (32 * q);
+            for (int a = 0; a < W; a++) {
+              if ((a & 3) == 0) a0 = fmaf(-ud[q][a], y[a], a0);
+              else if ((a & 3) == 1) a1 = fmaf(-ud[q][a], y[a], a1);
+              else if ((a & 3) == 2) a2 = fmaf(-ud[q][a], y[a], a2);
+              else a3 = fmaf(-ud[q][a], y[a], a3);
             }
-            viol &= range;
-            if (viol != 0) {
-              // rare (at most once per contact and solve): dense update, any group
-              const int v = MK::first(viol);
-              float dv = __shfl_sync(FULL, t[0], v & 31);
-              if (NR > 1) {
-                const float d1 = __shfl_sync(FULL, t[NR - 1], v & 31);
-                dv = v < 32 ? dv : d1;
-              }
-              DenseRow<CH> p;
-              p.load(crow + (3 * v) * RL::kRow, contact_group(ends03, v));
-#pragma unroll
-              for (int a = 0; a < W; a++) y[a] = fmaf(p.u[a], dv, y[a]);
-              sm.lam[v].x = dv;
-              act |= MK::bit(v);
-              const float rr = dv * p.s;
-              res = fmaxf(res, rr * rr);
-              lo = v + 1;
-              continue;
-            }
+            t[q] = (a0 + a1) + (a2 + a3);
+            viol |= (mask_t)__ballot_sync(FULL, t[q] > 0.f) << (32 * q);
           }
-          if (nxt >= end) break;   // G == kLegs: everything up to nc has been screened
-          float r[RL::kRow];
-          load_row(crow + (3 * nxt) * RL::kRow, r);
-          const float lam_n = sm.lam[nxt].x;
-          const float sum = fmaxf(lam_n + row_gap<CH, G>(r, y, 0.f), 0.f);
-          const float d = sum - lam_n;
-          sm.lam[nxt].x = sum;
-          row_axpy<CH, G>(r, d, y);
-          const float rr = d * r[RL::kS];
-          res = fmaxf(res, rr * rr);
-          rem &= rem - 1;
-          lo = nxt + 1;
+          viol &= range;
+          if (viol != 0) {
+            // ---- promotion of contact v into slot k (rare) ----
+            const int v = MK::first(viol);
+            float dv = __shfl_sync(FULL, t[0], v & 31);
+            if (NR > 1) {
+              const float d1 = __shfl_sync(FULL, t[NR - 1], v & 31);
+              dv = v < 32 ? dv : d1;
+            }
+            // shift entries [k, n_act) up by one; lane j moves the same words of every entry
+            for (int s = n_act - 1; s >= k; s--)
+              for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
+            __syncwarp();
+            // the owner lane builds the contact's three rows (the friction pair for the first time)
+            if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv);
+            act |= MK::bit(v);
+            n_act++;
+            __syncwarp();
+            // ranges of every entry and of the tail
+            for (int s = lane; s < n_act; s += 32) {
+              const int idx = __float_as_int(sm.ent[s][AL::kMeta + 3]);
+              const int prev = s > 0 ? __float_as_int(sm.ent[s - 1][AL::kMeta + 3]) : -1;
+              const mask_t m = MK::below(idx) & ~MK::below(prev + 1);
+              sm.ent[s][AL::kMeta + 4] = __uint_as_float((uint32_t)m);
+              sm.ent[s][AL::kMeta + 5] = __uint_as_float((uint32_t)((uint64_t)m >> 32));
+            }
+            tail_range = all & ~MK::below(MK::last(act) + 1);
+            __syncwarp();
+            float pr[AL::NW];
+            load_row(&sm.ent[k][0], pr);
+#pragma unroll
+            for (int a = 0; a < W; a++) y[a] = fmaf(pr[a], dv, y[a]);
+            const float rr = dv * pr[W + 1];
+            res = fmaxf(res, rr * rr);
+            k++;
+            continue;
+          }
         }
-      };
-      normal_group(IntC<0>());
-      normal_group(IntC<1>());
-      normal_group(IntC<2>());
-      normal_group(IntC<3>());
-      normal_group(IntC<4>());
+        if (at_end) break;
+        const float lam_n = m0.x;
+        const float sum = fmaxf(dense_gap<W>(nr, y, lam_n), 0.f);
+        const float d = sum - lam_n;
+        sm.ent[k][AL::kMeta] = sum;
+#pragma unroll
+        for (int a = 0; a < W; a++) y[a] = fmaf(nr[a], d, y[a]);
+        const float rr = d * nr[W + 1];
+        res = fmaxf(res, rr * rr);
+        k++;
+      }
 
       // ---- friction pairs of the contacts that can hold friction ----
       // both rows on the same velocity, radial projection onto the disc of radius
       // mu * lambda_n (resolveConeFrictionConstraintRows)
-      auto friction_group = [&](auto gtag) {
-        constexpr int G = decltype(gtag)::value;
-        const int begin = G > 0 ? (int)((ends03 >> (8 * (G - 1))) & 255u) : 0;
-        const int end = G < kLegs ? (int)((ends03 >> (8 * G)) & 255u) : nc;
-        for (mask_t fr = act & MK::below(end) & ~MK::below(begin); fr != 0; fr &= fr - 1) {
-          const int c = MK::first(fr);
-          float fa[RL::kRow], fb[RL::kRow];
-          load_row(crow + (3 * c + 1) * RL::kRow, fa);
-          load_row(crow + (3 * c + 2) * RL::kRow, fb);
-          const float4 l4 = sm.lam[c];
-          float sa = row_gap<CH, G>(fa, y, l4.y), sb = row_gap<CH, G>(fb, y, l4.z);
-          const float limit = fa[RL::kX] * l4.x;                   // mu * lambda_n, true units
-          const float ta = sa * fa[RL::kIs], tb = sb * fb[RL::kIs];  // true units
-          const float n2 = fmaf(ta, ta, fmaf(tb, tb, 1e-30f));
-          const float sc = n2 > limit * limit ? limit * fast_rsqrt(n2) : 1.f;
-          sa *= sc; sb *= sc;
-          const float da = sa - l4.y, db = sb - l4.z;
-          sm.lam[c].y = sa; sm.lam[c].z = sb;
-          row_axpy<CH, G>(fa, da, y);
-          row_axpy<CH, G>(fb, db, y);
-          const float r1 = da * fa[RL::kS], r2 = db * fb[RL::kS];
-          res = fmaxf(res, fmaxf(r1 * r1, r2 * r2));
-        }
-      };
-      if (act != 0) {
-        friction_group(IntC<0>());
-        friction_group(IntC<1>());
-        friction_group(IntC<2>());
-        friction_group(IntC<3>());
-        friction_group(IntC<4>());
+      for (int k = 0; k < n_act; k++) {
+        float *e = &sm.ent[k][0];
+        float fa[AL::FW], fb[AL::FW];
+        load_row(e + AL::kFA, fa);
+        load_row(e + AL::kFB, fb);
+        const float4 l4 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
+        float sa = dense_gap<W>(fa, y, l4.y), sb = dense_gap<W>(fb, y, l4.z);
+        const float limit = fa[W + 3] * l4.x;                  // mu * lambda_n, true units
+        const float ta = sa * fa[W + 2], tb = sb * fb[W + 2];  // true units
+        const float n2 = fmaf(ta, ta, fmaf(tb, tb, 1e-30f));
+        const float sc = n2 > limit * limit ? limit * fast_rsqrt(n2) : 1.f;
+        sa *= sc; sb *= sc;
+        const float da = sa - l4.y, db = sb - l4.z;
+        e[AL::kMeta + 1] = sa; e[AL::kMeta + 2] = sb;
+#pragma unroll
+        for (int a = 0; a < W; a++) y[a] = fmaf(fb[a], db, fmaf(fa[a], da, y[a]));
+        const float r1 = da * fa[W + 1], r2 = db * fb[W + 1];
+        res = fmaxf(res, fmaxf(r1 * r1, r2 * r2));
       }
     }
     it++;
     if (res <= C.res_thr) break;
   }
-  *n_active = MK::count(act);
+  *n_active = n_act;
   return it;
 }
 
 template <int CH, bool DBG>
 __global__ void __launch_bounds__(32)
 solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const uint32_t motor_mask,
-                  const int ndof_total, const int n_cand) {
+                  const int ndof_total, const int n_cand, const float margin) {
   typedef RowLayout<CH> RL;
+  typedef KinLayout<CH> KL;
+  typedef ActiveLayout<CH> AL;
   constexpr int W = 6 + kLegs * CH;   // dense width
+  constexpr unsigned FULL = 0xffffffffu;
   __shared__ __align__(16) WarpSolveSmem<CH> sm;
   const int lane = threadIdx.x;
   const int64_t env = blockIdx.x;
   const long long t_begin = clock64();
 
-  const uint32_t ends03 = B.hdr[env];
-  const int nc = (int)B.hdr[(int64_t)B.n + env];
-
-  // ---- stage: the env's row list -> smem, impulses = 0 ----
+  // ---- the environment's record -> smem ----
   {
-    const float4 *src = reinterpret_cast<const float4 *>(B.rows + env * (RL::kSlots * RL::kRow));
-    float4 *dst = reinterpret_cast<float4 *>(&sm.row[0][0]);
-    const int n4 = (RL::kMotorSlots + 3 * nc) * (RL::kRow / 4);
-    for (int i = lane; i < n4; i += 32) dst[i] = __ldcg(src + i);
-    for (int i = lane; i < nc; i += 32) sm.lam[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 *src = reinterpret_cast<const float4 *>(B.kin + env * KL::kSize);
+    float4 *dst = reinterpret_cast<float4 *>(sm.kin);
+    for (int i = lane; i < KL::kSize / 4; i += 32) dst[i] = __ldcg(src + i);
+  }
+  __syncwarp();
+
+  // ---- contact detection: support points inside the breaking threshold, in
+  // Bullet's order (by body, then by support point), capped at max_contacts ----
+  int nc = 0;
+  {
+    constexpr int kRounds = kMaxCand / 32;
+    uint32_t hits[kRounds];
+#pragma unroll
+    for (int i = 0; i < kRounds; i++) {
+      const int c = lane + 32 * i;
+      bool hit = false;
+      if (c < n_cand) hit = cand_distance<CH>(sm.kin, load_cand(B.cand_tab, c), margin) < C.breaking;
+      hits[i] = __ballot_sync(FULL, hit);
+    }
+    int before = 0;
+#pragma unroll
+    for (int i = 0; i < kRounds; i++) {
+      const int rank = before + __popc(hits[i] & ((1u << lane) - 1u));
+      if (((hits[i] >> lane) & 1u) && rank < C.max_contacts) sm.list[rank] = lane + 32 * i;
+      before += __popc(hits[i]);
+    }
+    nc = min(before, C.max_contacts);
   }
   __syncwarp();
 
   float y[W], mlam[kLegs * CH];
   int it = 0, n_active = 0;
   if (motor_mask != 0 || nc > 0) {
-    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, motor_mask, ends03, nc, lane, y, mlam, &n_active);
-    else it = warp_solve<CH, 2>(C, sm, motor_mask, ends03, nc, lane, y, mlam, &n_active);
+    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, motor_mask, nc, lane, y, mlam, &n_active);
+    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, motor_mask, nc, lane, y, mlam, &n_active);
   } else {
 #pragma unroll
     for (int a = 0; a < W; a++) y[a] = 0.f;
@@ -404,9 +398,10 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     if (B.dbg_normal_force) {
       for (int c = lane; c < n_cand; c += 32) B.dbg_normal_force[(int64_t)c * B.n + env] = 0.f;
       __syncwarp();
-      for (int i = lane; i < nc; i += 32) {
-        const float *nr = &sm.row[RL::kMotorSlots + 3 * i][0];
-        B.dbg_normal_force[(int64_t)(int)nr[RL::kX] * B.n + env] = sm.lam[i].x * nr[RL::kIs] * C.inv_dt;
+      for (int k = lane; k < n_active; k += 32) {
+        const float *e = &sm.ent[k][0];
+        const int cand = __float_as_int(e[AL::kMeta + 6]);
+        B.dbg_normal_force[(int64_t)cand * B.n + env] = e[AL::kMeta] / e[W + 1] * C.inv_dt;
       }
     }
     if (B.dbg_motor_torque && lane == 0) {
@@ -417,7 +412,8 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
 #pragma unroll
       for (int j = 0; j < kLegs * CH; j++) {
         if ((motor_mask >> j) & 1u) {
-          if (d < ndof_total) B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * sm.row[j][RL::kIs] * C.inv_dt;
+          if (d < ndof_total)
+            B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * sm.kin[KL::kMotor + j * RL::kRow + RL::kIs] * C.inv_dt;
           d++;
         }
       }
