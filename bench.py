@@ -65,6 +65,20 @@ def hbm_peak():
   return 6650.0, 'fallback'
 
 
+def ncu_traffic(kernel, n_envs):
+  """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the
+  committed `ncu --set full` capture (profiles/traffic.json, taken at 4096 envs with
+  ncu's cold caches); None for any other batch size."""
+  p = os.path.join(ROOT, 'profiles', 'traffic.json')
+  try:
+    t = json.load(open(p))
+    if int(t.get('envs', -1)) == int(n_envs):
+      return t['dram_bytes_per_launch'].get(kernel)
+  except Exception:
+    pass
+  return None
+
+
 # ---- clocks under load -------------------------------------------------------------
 class ClockSampler(threading.Thread):
   REASONS = [(0x8, 'hw_slowdown'), (0x40, 'hw_thermal_slowdown'), (0x20, 'sw_thermal_slowdown'),
@@ -289,7 +303,7 @@ def main():
     e2e_value = world * n * e2e_steps / (max(e2e_ms, e2e_wall_ms) * 1e-3)
     peak, peak_kind = hbm_peak()
     step_ms = float(per_step_ms.mean())
-    names = ['setup_kernel', 'solve_kernel', 'finish_kernel']
+    names = ['setup_kernel', 'solve_warp_kernel', 'finish_kernel']
     dom = int(np.argmax(phase_ms))
     launch_ms = phase_ms[dom]
     achieved = BYTES_PER_ENV_STEP * n / (launch_ms * 1e-3) / 1e9
@@ -301,10 +315,10 @@ def main():
                    'program': 'TorsoIMU+MotorEncoder, 1xUprightReward, PerpetualTermination',
                    'actions': 'U(-2pi,2pi)^12 fresh each step, generated on device outside the timed spans',
                    'l2': 'flushed between timed steps (256 MiB fill)' if flush is not None else 'not flushed',
-                   'block_threads': env.client.block_size(), 'solver_envs_per_warp': env.client.solver_lanes(),
+                   'block_threads': env.client.block_size(), 'solver': 'one warp per environment',
                    'timing': 'CUDA events around every step on the launching stream, summed; max over ranks'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': None, 'peak_source': peak_kind,
+                     'frac': achieved / peak, 'traffic': ncu_traffic(names[dom], n), 'peak_source': peak_kind,
                      'bytes_per_env_step': BYTES_PER_ENV_STEP, 'kernel': names[dom],
                      'launch_ms_mean': launch_ms,
                      'kernels_ms_mean': dict(zip(names, phase_ms)), 'kernel_share_of_step': launch_ms / sum(phase_ms),
