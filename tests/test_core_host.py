@@ -77,3 +77,22 @@ def test_torque_mode_and_free_flight(world):
     assert d['n_contacts'] == 0 and d['iterations'] == 0
     np.testing.assert_allclose(got, want, atol=1e-10)
     s = want
+
+
+def test_mmr_v4_model_float64_core_tracks_oracle():
+  """BASELINE configs[3] model (solo8_URDF_v4: 10 dof, hind chains of 3 joints ->
+  the CH = 3 instantiation of the core)."""
+  blob, model, config = H.model_and_config('solo8_mmr_v4', dt=1 / 240.)
+  assert model.ndof == 10 and list(model.chain_len)[:4] == [3, 3, 2, 2]
+  orc = H.oracle(model, config)
+  a = orc.settle(np.zeros(10))
+  rng = np.random.RandomState(7)
+  worst, its = 0.0, []
+  for k in range(200):
+    act = rng.uniform(-2 * np.pi, 2 * np.pi, 10)
+    c, d = H.hostsim_step(model, config, a, act, use_double=True)
+    a = orc.step(a, act)
+    its.append(d['iterations'])
+    worst = max(worst, np.abs(a - c).max())
+  assert worst < 1e-9, worst
+  assert max(its) > 10

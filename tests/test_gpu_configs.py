@@ -1,0 +1,209 @@
+"""GPU parity for the rest of BASELINE.json's configs (run with -m gpu on a B200):
+the MMR v4 model (configs[3]: 10 joints, chains of 3 -> the CH = 3 kernels), torque
+control with 4 substeps per action (configs[4]), HomePositionReward + UprightReward
+with time-based termination and in-kernel auto reset (configs[2]), environments
+with more than 32 contacts (the two-rows-per-lane path of the solver warp), and the
+host-buffer entry (solo_step_host) against the device-buffer one.  All through the
+C-ABI; the checker is the double-precision oracle (oracle/)."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from gym_solo_b200 import _abi
+from helpers import START_TARGETS, model_and_config, oracle, state_errors
+from oracle import solo_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+TOL = dict(base_pos=1e-5, base_rot=1e-4, base_lin=1e-3, base_ang=2e-3, q=1e-4, qd=1e-3)
+# The v4 model's distal links are a few grams: the float32 leg blocks are worse conditioned and
+# the joint-rate error of one step reaches 2e-2 rad/s in the float32 HOST build of the core too
+# (tests/test_core_host.py arithmetic; float64 agrees with the oracle to 1e-9), so the stated
+# per-step tolerance for this model is 5e-2 rad/s on joint rates, 2e-4 rad on joint angles.
+TOL_V4 = dict(base_pos=1e-5, base_rot=1e-4, base_lin=1e-3, base_ang=2e-3, q=2e-4, qd=5e-2)
+# torque mode: nothing damps the 50 g legs, joint rates of tens of rad/s are normal; four
+# chained float32 substeps are held to 4 x the single-step budget, 1e-2 rad/s on joint rates
+TOL_TORQUE4 = dict(base_pos=4e-5, base_rot=4e-4, base_lin=4e-3, base_ang=8e-3, q=4e-4, qd=1e-2)
+
+
+def make_client(n, name='solo8v2', **cfg):
+  from gym_solo_b200.client import BatchedClient
+  blob, model, config = model_and_config(name, **cfg)
+  return BatchedClient(blob, model, config, n, 'cuda:0'), model, config
+
+
+def oracle_pool(model, config, n_states, n_api, seed, targets, stride=5, low=-2 * np.pi, high=2 * np.pi,
+                start=200, hold=15):
+  o = oracle(model, config)
+  rng = np.random.RandomState(seed)
+  s = o.initial_state()
+  out, k, a = [], 0, targets
+  while len(out) < n_states:
+    if k >= start and k % hold == 0:
+      a = rng.uniform(low, high, n_api)
+    s = o.step(s, a)
+    if k % stride == 0:
+      out.append(s.copy())
+    k += 1
+  return np.stack(out)
+
+
+def test_mmr_v4_model_single_step_parity():
+  """configs[3]: examples/solo8_mmr (solo8_URDF_v4.urdf): 10 dof, hind chains of 3."""
+  n = 192
+  c, model, config = make_client(n, name='solo8_mmr_v4', dt=1.0 / 240.0)
+  assert model.ndof == 10 and model.n_api == 10
+  states = oracle_pool(model, config, n, 10, seed=11, targets=np.zeros(10))
+  rng = np.random.RandomState(12)
+  actions = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 10))
+  nf_dev, mt_dev = c.enable_debug(True)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  nf = nf_dev.t().double().cpu().numpy()
+  o = oracle(model, config)
+  want = np.zeros_like(states)
+  nf_want = np.zeros_like(nf)
+  for i in range(n):
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i], d = o.step(s32, a32, diag=True)
+    nf_want[i] = d['normal_force'][:nf.shape[1]]
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL_V4.items():
+    assert err[k] <= tol, (k, err)
+  assert np.all(np.abs(nf - nf_want) <= 0.05 + 1e-3 * np.abs(nf_want)), np.abs(nf - nf_want).max()
+  assert nf_want.max() > 1.0
+  c.disconnect()
+
+
+def test_torque_control_four_substeps():
+  """configs[4]: torque control, 4 physics substeps per action (one solo_step =
+  4 x (setup, solve, finish); the epilogue runs on the last)."""
+  n = 128
+  c, model, config = make_client(n, dt=1.0 / 240.0, control_mode=_abi.CONTROL_TORQUE, num_substeps=4)
+  states = oracle_pool(model, config, n, 12, seed=21, targets=np.zeros(12), low=-0.1, high=0.1, start=100, hold=10)
+  rng = np.random.RandomState(22)
+  actions = rng.uniform(-2.5, 2.5, (n, 12))       # beyond the 2 N m limit: clamped
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'), n_steps=4)
+  got = c.get_state().double().cpu().numpy()
+  o = oracle(model, config)
+  want = np.zeros_like(states)
+  for i in range(n):
+    s = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i] = o.step(s, a32)      # the oracle runs config.num_substeps physics steps per action
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL_TORQUE4.items():
+    assert err[k] <= tol, (k, err)
+  c.disconnect()
+
+
+def test_more_than_32_contacts():
+  """The robot dropped flat on its belly with the legs folded: > 32 support points
+  inside the breaking threshold, i.e. two normal rows per lane in the solver warp."""
+  n = 64
+  c, model, config = make_client(n, dt=1.0 / 240.0)
+  o = oracle(model, config)
+  rng = np.random.RandomState(31)
+  states, ncs = [], []
+  s = o.initial_state(pos=(0., 0., 0.06))
+  folded = START_TARGETS
+  k = 0
+  while len(states) < n and k < 4000:
+    a = folded + (rng.uniform(-0.3, 0.3, 12) if k % 10 == 0 else 0)
+    s, d = o.step(s, a, diag=True)
+    if d['n_contacts'] > 32:
+      states.append(s.copy()); ncs.append(d['n_contacts'])
+    k += 1
+  assert len(states) >= 8, 'pool has no > 32-contact states (max seen %s)' % (max(ncs) if ncs else 0)
+  states = np.stack((states * (n // len(states) + 1))[:n])
+  actions = np.tile(folded, (n, 1)) + rng.uniform(-0.5, 0.5, (n, 12))
+  nf_dev, _ = c.enable_debug(True)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  nf = nf_dev.t().double().cpu().numpy()
+  want = np.zeros_like(states)
+  nf_want = np.zeros_like(nf)
+  worst_nc = 0
+  for i in range(n):
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i], d = o.step(s32, a32, diag=True)
+    nf_want[i] = d['normal_force'][:nf.shape[1]]
+    worst_nc = max(worst_nc, d['n_contacts'])
+  assert worst_nc > 32
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL.items():
+    assert err[k] <= tol, (k, err)
+  assert np.all(np.abs(nf - nf_want) <= 0.05 + 1e-3 * np.abs(nf_want)), np.abs(nf - nf_want).max()
+  st = c.solver_stats().cpu().numpy()
+  assert st[1].max() > 32           # the kernel saw them too
+  c.disconnect()
+
+
+def _env(n, auto_reset, max_steps):
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  cfg = Solo8VanillaConfig()
+  cfg.dt = 1.0 / 240.0
+  env = Solo8VanillaEnv(config=cfg, num_envs=n, device='cuda:0', auto_reset=auto_reset)
+  env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+  env.obs_factory.register_observation(obs.MotorEncoder(env.robot))
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    env.reward_factory.register_reward(1, rewards.UprightReward(env.robot))
+    env.reward_factory.register_reward(1, rewards.HomePositionReward(env.robot))
+  env.termination_factory.register_termination(termination.TimeBasedTermination(max_steps))
+  return env
+
+
+def test_home_position_reward_time_termination_auto_reset():
+  """configs[2]: 1 x Upright + 1 x HomePosition, TimeBasedTermination, snapshot
+  auto reset inside the step kernel; rewards against the oracle's
+  restatement of the reference's reward classes on the kernel's own states."""
+  n, T = 96, 4
+  env = _env(n, True, T)
+  first = env.reset()
+  model = env._model
+  g = torch.Generator(device='cuda:0').manual_seed(41)
+  for k in range(1, 2 * (T + 1) + 1):
+    act = (torch.rand((n, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    o, r, d, info = env.step(act)
+    fire = (k % (T + 1) == 0)      # done on call max_step_delta + 1 (termination.py:59-83)
+    assert bool(d.all()) == fire and bool(d.any()) == fire, (k, d.sum())
+    assert 'terminal_observation' in info
+    if fire:
+      # the returned row is the first observation of the new episode; the terminal one is in info
+      assert torch.allclose(o, first, atol=1e-6)
+      assert not torch.allclose(info['terminal_observation'], first, atol=1e-3)
+      assert torch.allclose(env.get_state(), env.get_state()[0:1].expand(n, -1))
+    else:
+      st = env.get_state().double().cpu().numpy()
+      view = so.StateView(st, model)
+      want = so.upright_reward(view) + so.home_position_reward(view)
+      assert np.abs(r.double().cpu().numpy() - want).max() <= 2e-3
+      assert torch.equal(o, info['terminal_observation'])
+  stats = env.episode_statistics().cpu().numpy()
+  assert stats[2] == 2 * n          # two finished episodes per env
+  env.close()
+
+
+def test_step_host_matches_device_step():
+  """solo_step_host (numpy in / numpy out, H2D + D2H inside) == solo_step."""
+  n = 200
+  a_env, b_env = _env(n, False, 1000), _env(n, False, 1000)
+  a_env.reset(); b_env.reset()
+  rng = np.random.RandomState(51)
+  for _ in range(5):
+    act = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12)).astype(np.float32)
+    o1, r1, d1, _ = a_env.step(torch.tensor(act, device='cuda:0'))
+    o2, r2, d2, _ = b_env.step_host(act)
+    assert np.array_equal(o1.cpu().numpy(), o2)
+    assert np.array_equal(r1.cpu().numpy(), r2)
+    assert np.array_equal(d1.cpu().numpy(), d2)
+  a_env.close(); b_env.close()
