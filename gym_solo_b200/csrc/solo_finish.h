@@ -18,6 +18,26 @@ SOLO_HD void finish_step(const ModelT<T> &M, const ConfigT<T> &C, EnvState<T, CH
 #pragma unroll
       for (int j = 0; j <= i; j++) S[i][j] = fac[(k++) * fac_stride];
   }
+  // every factor is fetched before the first use: the loads are independent, so
+  // their latencies overlap instead of adding up phase by phase
+  T Bh[kLegs][CH][6], E[kLegs][CH][CH], vb0[6], vl0[kLegs][CH];
+#pragma unroll
+  for (int i = 0; i < 6; i++) vb0[i] = fac[(FL::kVb + i) * fac_stride];
+#pragma unroll
+  for (int l = 0; l < kLegs; l++) {
+    const int base = FL::kLeg + l * FL::kLegSize;
+#pragma unroll
+    for (int i = 0; i < CH; i++)
+#pragma unroll
+      for (int a = 0; a < 6; a++) Bh[l][i][a] = fac[(base + i * 6 + a) * fac_stride];
+    int k = base + CH * 6;
+#pragma unroll
+    for (int i = 0; i < CH; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) E[l][i][j] = fac[(k++) * fac_stride];
+#pragma unroll
+    for (int i = 0; i < CH; i++) vl0[l][i] = fac[(FL::kVl + l * CH + i) * fac_stride];
+  }
   T vb[6], dvb[6];
 #pragma unroll
   for (int i = 0; i < 6; i++) {
@@ -25,34 +45,25 @@ SOLO_HD void finish_step(const ModelT<T> &M, const ConfigT<T> &C, EnvState<T, CH
 #pragma unroll
     for (int k = i; k < 6; k++) t += S[k][i] * yb[k];
     dvb[i] = t;
-    vb[i] = m_clamp(fac[(FL::kVb + i) * fac_stride] + t, -C.max_vel, C.max_vel);
+    vb[i] = m_clamp(vb0[i] + t, -C.max_vel, C.max_vel);
   }
 #pragma unroll
   for (int l = 0; l < kLegs; l++) {
-    const int base = FL::kLeg + l * FL::kLegSize;
     T t[CH];
 #pragma unroll
     for (int i = 0; i < CH; i++) {
       T u = yl[l][i];
 #pragma unroll
-      for (int a = 0; a < 6; a++) u -= fac[(base + i * 6 + a) * fac_stride] * dvb[a];
+      for (int a = 0; a < 6; a++) u -= Bh[l][i][a] * dvb[a];
       t[i] = u;
-    }
-    T E[CH][CH];
-    {
-      int k = base + CH * 6;
-#pragma unroll
-      for (int i = 0; i < CH; i++)
-#pragma unroll
-        for (int j = 0; j <= i; j++) E[i][j] = fac[(k++) * fac_stride];
     }
 #pragma unroll
     for (int i = 0; i < CH; i++) {
       T dv = 0;
 #pragma unroll
-      for (int k = i; k < CH; k++) dv += E[k][i] * t[k];
+      for (int k = i; k < CH; k++) dv += E[l][k][i] * t[k];
       const bool a = (l < M.n_legs) && (i < M.chain_len[l]);
-      const T v = a ? m_clamp(fac[(FL::kVl + l * CH + i) * fac_stride] + dv, -C.max_vel, C.max_vel) : T(0);
+      const T v = a ? m_clamp(vl0[l][i] + dv, -C.max_vel, C.max_vel) : T(0);
       s.qd[l][i] = v;
       s.q[l][i] += dt * v;
     }
