@@ -169,6 +169,12 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   const mask_t all = MK::below(nc);
   mask_t act = 0;          // contacts that have carried a normal impulse (= the entries of sm.ent)
   mask_t tail_range = all; // speculative rows behind the last active contact
+  // Screening budget.  Rows are unit vectors, so an update of size d moves any gap
+  // b' - u.yh by at most |d|.  After an exact screen the smallest distance of a
+  // speculative row from coming alive is known; until the |d| of the updates since
+  // then add up to it, no speculative row can be alive and the screens are skipped
+  // (exactly: a skipped screen would have found nothing).
+  float budget = 0.f;
   int n_act = 0;
   int it = 0;
   for (; it < C.iters;) {
@@ -199,6 +205,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         for (int k = 0; k < CH; k++) y[6 + l * CH + k] = fmaf(r[6 + k], d, y[6 + l * CH + k]);
         const float rr = d * r[RL::kS];
         res = fmaxf(res, rr * rr);
+        budget -= fabsf(d);
       };
       if (it & 1) {
 #pragma unroll
@@ -223,9 +230,10 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         const float4 m0 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
         const float4 m1 = *reinterpret_cast<const float4 *>(e + AL::kMeta + 4);
         const mask_t range = at_end ? tail_range : MK::make(__float_as_uint(m1.x), __float_as_uint(m1.y));
-        if (range != 0) {
+        if (range != 0 && budget <= 0.f) {
           mask_t viol = 0;
           float t[NR];
+          float slack = 3.0e38f;
 #pragma unroll
           for (int q = 0; q < NR; q++) {
             float a0 = ub[q], a1 = 0.f, a2 = 0.f, a3 = 0.f;
@@ -237,9 +245,12 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
               else a3 = fmaf(-ud[q][a], y[a], a3);
             }
             t[q] = (a0 + a1) + (a2 + a3);
+            // distance from coming alive, speculative rows only (absent rows sit at 1)
+            if (((act >> (lane + 32 * q)) & 1) == 0) slack = fminf(slack, fmaxf(-t[q], 0.f));
             viol |= (mask_t)__ballot_sync(FULL, t[q] > 0.f) << (32 * q);
           }
           viol &= range;
+          budget = 0.999f * __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(slack)));
           if (viol != 0) {
             // ---- promotion of contact v into slot k (rare) ----
             const int v = MK::first(viol);
@@ -273,6 +284,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
             for (int a = 0; a < W; a++) y[a] = fmaf(pr[a], dv, y[a]);
             const float rr = dv * pr[W + 1];
             res = fmaxf(res, rr * rr);
+            budget = 0.f;   // a row elsewhere may be alive too: screen again
             k++;
             continue;
           }
@@ -286,6 +298,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         for (int a = 0; a < W; a++) y[a] = fmaf(nr[a], d, y[a]);
         const float rr = d * nr[W + 1];
         res = fmaxf(res, rr * rr);
+        budget -= fabsf(d);
         k++;
       }
 
@@ -310,6 +323,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         for (int a = 0; a < W; a++) y[a] = fmaf(fb[a], db, fmaf(fa[a], da, y[a]));
         const float r1 = da * fa[W + 1], r2 = db * fb[W + 1];
         res = fmaxf(res, fmaxf(r1 * r1, r2 * r2));
+        budget -= fabsf(da) + fabsf(db);
       }
     }
     it++;
