@@ -62,7 +62,7 @@ class BatchedClient:
     self.snapshot = torch.zeros((self.sdim,), dtype=torch.float32, device=dev)
     self.stats = torch.zeros((4, self.n), dtype=torch.float32, device=dev)
     self.diag = torch.zeros((4,), dtype=torch.int64, device=dev)
-    # solver scratch: constraint rows, mass-matrix factors, yh, contact headers
+    # solver scratch: per-env records for the solver warp, mass-matrix factors, yh, support points
     nbytes = int(self.lib.solo_scratch_bytes(self.handle))
     if nbytes < 0:
       raise _lib.SoloError('solo_scratch_bytes failed')

@@ -156,8 +156,9 @@ int solo_destroy(SoloHandle h);
 int solo_set_program(SoloHandle h, const SoloProgram *program);
 /* len(observation_space.low) for the current program (obs.py:161-190). */
 int solo_obs_dim(SoloHandle h);
-/* Bytes of solver scratch the caller must bind (256-byte aligned): constraint
- * rows, mass-matrix factors, solver output and contact headers of one step. */
+/* Bytes of solver scratch the caller must bind (256-byte aligned): the
+ * per-environment records setup leaves for the solver warp, mass-matrix
+ * factors, solver output and the support-point table of one step. */
 int64_t solo_scratch_bytes(SoloHandle h);
 
 /* Bind caller-owned device buffers.  state_dev: float[SOLO_STATE_DIM][n_envs];
@@ -220,9 +221,8 @@ int solo_block_size(SoloHandle h);
  * inside the bound scratch: PGS iterations, contact points, contact points that
  * carried an impulse, SM cycles spent in the solve. */
 int solo_solver_stats(SoloHandle h, const float **stats_dev);
-/* 0: the solver runs one warp per environment (default); otherwise the
- * environments per warp of the lane-per-environment solver (SOLO_SOLVER=lane,
- * SOLO_LANES). */
+/* Environments per warp of the solver kernel: always 0 = one WARP per
+ * environment (kept for callers of the earlier lane-per-environment solver). */
 int solo_solver_lanes(SoloHandle h);
 /* Live per-kernel timing (bench.py roofline): while enabled every physics step
  * records CUDA events on the launching stream around its three kernels;
