@@ -185,10 +185,15 @@ class BatchedClient:
 
   def bind_staging(self, obs_dim):
     dev = self.device
-    self._staging = (torch.empty((self.n, self.n_api), dtype=torch.float32, device=dev),
-                     torch.empty((self.n, obs_dim), dtype=torch.float32, device=dev),
-                     torch.empty((self.n,), dtype=torch.float32, device=dev),
-                     torch.empty((self.n,), dtype=torch.uint8, device=dev))
+    # observations | reward | done in ONE allocation: solo_step_host then brings the
+    # three results back with a single device->host copy when the host side is laid
+    # out the same way (Solo8VanillaEnv.step_host does that)
+    n, nb = self.n, self.n * (obs_dim * 4 + 4 + 1)
+    self._staging_out = torch.empty((nb,), dtype=torch.uint8, device=dev)
+    self._staging = (torch.empty((n, self.n_api), dtype=torch.float32, device=dev),
+                     self._staging_out[:n * obs_dim * 4].view(torch.float32).view(n, obs_dim),
+                     self._staging_out[n * obs_dim * 4:n * obs_dim * 4 + n * 4].view(torch.float32),
+                     self._staging_out[n * obs_dim * 4 + n * 4:])
     _lib.check(self.lib.solo_bind_staging(self.handle, *[_ptr(t) for t in self._staging]), self.handle)
 
   def step_host(self, actions_np, scale, obs_np, reward_np, done_np):

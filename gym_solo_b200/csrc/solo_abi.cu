@@ -402,9 +402,17 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, 
   if (e != cudaSuccess) return cuda_fail(h, e, "H2D actions");
   int rc = solo_step(h, h->st_actions, action_scale, h->st_obs, h->st_reward, h->st_done, nullptr, stream);
   if (rc) return rc;
-  e = cudaMemcpyAsync(obs_host, h->st_obs, n * h->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, h->st_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(done_host, h->st_done, n, cudaMemcpyDeviceToHost, st);
+  const size_t ob = n * h->obs_dim * sizeof(float), rb = n * sizeof(float);
+  const bool packed = (char *)h->st_reward == (char *)h->st_obs + ob && (char *)h->st_done == (char *)h->st_reward + rb &&
+                      (char *)reward_host == (char *)obs_host + ob && (char *)done_host == (char *)reward_host + rb;
+  if (packed) {
+    // staging and host buffers are both laid out obs | reward | done: one copy
+    e = cudaMemcpyAsync(obs_host, h->st_obs, ob + rb + n, cudaMemcpyDeviceToHost, st);
+  } else {
+    e = cudaMemcpyAsync(obs_host, h->st_obs, ob, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, h->st_reward, rb, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(done_host, h->st_done, n, cudaMemcpyDeviceToHost, st);
+  }
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) return cuda_fail(h, e, "D2H results");
   return SOLO_OK;

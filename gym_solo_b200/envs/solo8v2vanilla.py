@@ -197,12 +197,14 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     c.set_program(plan['program'], token=plan['token'])
     if self._host is None or self._host['dim'] != plan['obs_dim']:
       c.bind_staging(plan['obs_dim'])
-      pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
-      self._host = dict(dim=plan['obs_dim'],
-                        act=pin((c.n, c.n_api), torch.float32),
-                        obs=pin((c.n, plan['obs_dim']), torch.float32),
-                        rew=pin((c.n,), torch.float32),
-                        done=pin((c.n,), torch.uint8))
+      # one pinned block laid out as the device staging (obs | reward | done): a single D2H
+      d, n = plan['obs_dim'], c.n
+      out = torch.empty((n * (d * 4 + 4 + 1),), dtype=torch.uint8).pin_memory()
+      self._host = dict(dim=d, out=out,
+                        act=torch.empty((n, c.n_api), dtype=torch.float32).pin_memory(),
+                        obs=out[:n * d * 4].view(torch.float32).view(n, d),
+                        rew=out[n * d * 4:n * d * 4 + n * 4].view(torch.float32),
+                        done=out[n * d * 4 + n * 4:])
     h = self._host
     a = h['act'].numpy()
     a[...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
