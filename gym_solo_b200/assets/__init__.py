@@ -8,6 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _BLOBS = {
     'assets/solo8v2/solo.urdf': 'solo8v2.json',
     'assets/solo8_URDF_v4/solo8_URDF_v4.urdf': 'solo8_mmr_v4.json',
+    'assets/solo8_URDF_v3/solo8_URDF_v3.urdf': 'solo8_urdf_v3.json',
 }
 
 

@@ -79,10 +79,12 @@ def test_torque_mode_and_free_flight(world):
     s = want
 
 
-def test_mmr_v4_model_float64_core_tracks_oracle():
+@pytest.mark.parametrize('name', ['solo8_mmr_v4', 'solo8_urdf_v3'])
+def test_mmr_v4_model_float64_core_tracks_oracle(name):
   """BASELINE configs[3] model (solo8_URDF_v4: 10 dof, hind chains of 3 joints ->
-  the CH = 3 instantiation of the core)."""
-  blob, model, config = H.model_and_config('solo8_mmr_v4', dt=1 / 240.)
+  the CH = 3 instantiation of the core) and the unreferenced v3 URDF the model
+  compiler also takes."""
+  blob, model, config = H.model_and_config(name, dt=1 / 240.)
   assert model.ndof == 10 and list(model.chain_len)[:4] == [3, 3, 2, 2]
   orc = H.oracle(model, config)
   a = orc.settle(np.zeros(10))

@@ -207,3 +207,76 @@ def test_step_host_matches_device_step():
     assert np.array_equal(r1.cpu().numpy(), r2)
     assert np.array_equal(d1.cpu().numpy(), d2)
   a_env.close(); b_env.close()
+
+
+def test_user_defined_plugins_run_unfused_and_match_the_fused_builtins():
+  """Observation / Reward / Termination subclasses written against the
+  client getters (the reference's extension point, README.md:26) keep working: the env
+  then runs the physics launches and evaluates the factories on batched tensors.  A
+  user-written copy of UprightReward / a base-height observation must agree with the
+  fused program on the same actions."""
+  from gym_solo_b200 import spaces
+  from gym_solo_b200.core import obs, rewards, termination
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+
+  class BaseHeight(obs.Observation):
+    def __init__(self, body_id):
+      self.robot = body_id
+
+    @property
+    def observation_space(self):
+      return spaces.Box(low=np.array([0.]), high=np.array([2.]))
+
+    @property
+    def labels(self):
+      return ['z']
+
+    def compute(self):
+      pos, _ = self.client.getBasePositionAndOrientation(self.robot)
+      return pos[:, 2:3]
+
+  class MyUpright(rewards.Reward):
+    def __init__(self, body_id):
+      self.robot = body_id
+
+    def compute(self):
+      _, quat = self.client.getBasePositionAndOrientation(self.robot)
+      pitch = self.client.getEulerFromQuaternion(quat)[:, 1]
+      return -2.0 * pitch / np.pi              # rewards.py:221-234
+
+  class Never(termination.Termination):
+    def reset(self, mask=None):
+      pass
+
+    def is_terminated(self):
+      return False
+
+  def make(user):
+    cfg = Solo8VanillaConfig()
+    cfg.dt = 1.0 / 240.0
+    env = Solo8VanillaEnv(config=cfg, num_envs=64, device='cuda:0')
+    env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+    if user:
+      env.obs_factory.register_observation(BaseHeight(env.robot))
+    with warnings.catch_warnings():
+      warnings.simplefilter('ignore', DeprecationWarning)
+      env.reward_factory.register_reward(1, MyUpright(env.robot) if user else rewards.UprightReward(env.robot))
+    env.termination_factory.register_termination(Never() if user else termination.PerpetualTermination())
+    env.reset()
+    return env
+
+  a, b = make(True), make(False)
+  assert a._build_plan() is None and b._build_plan() is not None     # unfused vs fused
+  g = torch.Generator(device='cuda:0').manual_seed(61)
+  for _ in range(6):
+    act = (torch.rand((64, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    oa, ra, da, ia = a.step(act)
+    ob, rb, db, ib = b.step(act)
+    assert oa.shape == (64, 10) and ob.shape == (64, 9)
+    assert ia['labels'][-1] == 'z'
+    assert torch.allclose(oa[:, :9].float(), ob, atol=1e-5)
+    assert torch.allclose(oa[:, 9].float(), a.get_state()[:, 2], atol=1e-6)
+    assert torch.allclose(ra.float(), rb, atol=1e-5)
+    assert not bool(da.any()) and not bool(db.any())
+    assert torch.equal(a.get_state(), b.get_state())                 # same physics either way
+  a.close(); b.close()
