@@ -43,6 +43,15 @@ WORKLOAD = ('Solo8VanillaEnv batched 4096 envs on 1xB200, position control, flat
             'dt=1/240 (BASELINE.json configs[1])')
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+  out = _REAL_STDOUT or sys.stdout
+  out.write(json.dumps(line) + '\n')
+  out.flush()
+
+
 def parse_args():
   ap = argparse.ArgumentParser()
   ap.add_argument('--gpus', type=int, default=1)
@@ -65,6 +74,18 @@ def hbm_peak():
   return 6650.0, 'fallback'
 
 
+def ncu_instructions(kernel, n_envs):
+  """smsp__inst_executed.sum of one launch of `kernel` from the same capture, or None."""
+  p = os.path.join(ROOT, 'profiles', 'traffic.json')
+  try:
+    t = json.load(open(p))
+    if int(t.get('envs', -1)) == int(n_envs):
+      return t['warp_instructions_per_launch'].get(kernel)
+  except Exception:
+    pass
+  return None
+
+
 def ncu_traffic(kernel, n_envs):
   """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the
   committed `ncu --set full` capture (profiles/traffic.json, taken at 4096 envs with
@@ -77,6 +98,17 @@ def ncu_traffic(kernel, n_envs):
   except Exception:
     pass
   return None
+
+
+def issue_util(kernel, n_envs, launch_ms, clocks):
+  """Secondary roofline for this latency/issue-bound path: warp instructions of one launch
+  (ncu capture) / issue slots the launch had (148 SMs x 4 schedulers x cycles at the sampled
+  SM clock).  None without a capture for this batch size."""
+  inst = ncu_instructions(kernel, n_envs)
+  mhz = clocks.get('sm_mhz') or clocks.get('sm_max_mhz')
+  if not inst or not mhz or launch_ms <= 0:
+    return None
+  return inst / (148 * 4 * launch_ms * 1e-3 * mhz * 1e6)
 
 
 # ---- clocks under load -------------------------------------------------------------
@@ -198,10 +230,17 @@ def reference_arm(args, rank):
       'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
       'gpu_launches': 0,
   }
-  print(json.dumps(line), flush=True)
+  emit(line)
 
 
 def main():
+  # stdout carries exactly ONE JSON line: native libraries (NCCL's version banner ...) write to
+  # file descriptor 1 behind Python's back, so fd 1 is pointed at stderr for the whole run and
+  # the line goes to a private duplicate of the original stdout
+  global _REAL_STDOUT
+  sys.stdout.flush()
+  _REAL_STDOUT = os.fdopen(os.dup(1), 'w')
+  os.dup2(2, 1)
   args = parse_args()
   rank = int(os.environ.get('RANK', '0'))
   world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -328,6 +367,7 @@ def main():
                      'step_ms_mean': step_ms, 'step_ms_p50': float(np.median(per_step_ms)),
                      'step_ms_max': float(per_step_ms.max()),
                      'whole_step_frac': BYTES_PER_ENV_STEP * n / (step_ms * 1e-3) / 1e9 / peak,
+                     'issue_slot_util': issue_util(names[dom], n, launch_ms, sampler.summary()),
                      'note': 'path is FP32-issue/latency bound, not HBM bound (SURVEY.md 8d)'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * n * 12 * 4,
                 'd2h_bytes_per_step': world * n * (21 * 4 + 4 + 1), 'steps': e2e_steps,
@@ -348,7 +388,7 @@ def main():
                               'sample': '%d envs x %d steps of the same workload (%.1f s), oracle port: '
                                         'C double physics on %d pthreads + numpy epilogue'
                                         % (c_envs, c_steps, ct, threads)}
-    print(json.dumps(line), flush=True)
+    emit(line)
   env.close()
   if world > 1:
     dist.barrier()

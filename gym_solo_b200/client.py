@@ -123,7 +123,18 @@ class BatchedClient:
     return self.state.t().contiguous()
 
   def set_snapshot(self, state):
-    self.snapshot.copy_(torch.as_tensor(np.asarray(state, dtype=np.float32)).to(self.device))
+    """state: [sdim] -- one reset state for every env (the reference's reset is
+    deterministic) -- or [N, sdim], one per env (solo_snapshot_layout)."""
+    t = torch.as_tensor(np.asarray(state, dtype=np.float32) if not torch.is_tensor(state) else state)
+    t = t.to(device=self.device, dtype=torch.float32)
+    per_env = t.dim() == 2
+    shape = (self.sdim, self.n) if per_env else (self.sdim,)
+    if tuple(self.snapshot.shape) != shape:
+      self.snapshot = torch.zeros(shape, dtype=torch.float32, device=self.device)
+      _lib.check(self.lib.solo_bind(self.handle, _ptr(self.state), _ptr(self.counters),
+                                    _ptr(self.snapshot), _ptr(self.stats), _ptr(self.scratch)), self.handle)
+    _lib.check(self.lib.solo_snapshot_layout(self.handle, 1 if per_env else 0), self.handle)
+    self.snapshot.copy_(t.t() if per_env else t)
 
   def settle_snapshot(self, start_targets_api, pos, euler, n_steps=500):
     """reset()'s settle (solo8v2vanilla.py:124-136) computed ONCE per (model,
@@ -132,6 +143,19 @@ class BatchedClient:
     cfg = _abi.SoloConfig.from_buffer_copy(self.config)
     cfg.control_mode = _abi.CONTROL_POSITION
     cfg.num_substeps = 1
+    if np.ndim(pos) == 2 or np.ndim(euler) == 2:
+      # start poses that differ per environment: the settle runs for the
+      # whole batch, one snapshot per env
+      pos_n = np.broadcast_to(np.asarray(pos, dtype=np.float64), (self.n, 3))
+      eul_n = np.broadcast_to(np.asarray(euler, dtype=np.float64), (self.n, 3))
+      full = BatchedClient(self.blob, self.model, cfg, self.n, self.device)
+      full.set_state(np.stack([full.initial_state(pos_n[i], eul_n[i]) for i in range(self.n)]))
+      a = torch.tensor(np.asarray(start_targets_api, dtype=np.float32), device=self.device)
+      full.simulate(a, n_steps=n_steps, broadcast=True)
+      snap = full.get_state()
+      full.disconnect()
+      self.set_snapshot(snap)
+      return snap.double().cpu().numpy()
     key = (_struct_key(self.model), _struct_key(cfg), tuple(float(x) for x in start_targets_api),
            tuple(pos), tuple(euler), n_steps, self.index)
     snap = _SNAPSHOT_CACHE.get(key)

@@ -240,6 +240,12 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
   return SOLO_OK;
 }
 
+int solo_snapshot_layout(SoloHandle h, int32_t per_env) {
+  if (!h) return SOLO_EINVAL;
+  h->B.snapshot_per_env = per_env ? 1 : 0;
+  return SOLO_OK;
+}
+
 int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev) {
   if (!h) return SOLO_EINVAL;
   h->B.diag = diag_dev;

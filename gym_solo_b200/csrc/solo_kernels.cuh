@@ -42,7 +42,7 @@ static_assert(sizeof(KParams) < 16384, "constant tables must fit the kernel para
 struct Buffers {
   float *state;              // [state_dim][n]
   int32_t *counters;         // [kMaxTermTerms][n]
-  const float *snapshot;     // [state_dim]
+  const float *snapshot;     // [state_dim], or [state_dim][n] when snapshot_per_env (solo_snapshot_layout)
   float *stats;              // [4][n] or null: running return, running length, last return, episodes
   unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, physics steps
   float *dbg_normal_force;   // [n_cand][n] or null
@@ -54,6 +54,7 @@ struct Buffers {
   float *kin;                // [n][KinLayout<CH>::kSize]: one contiguous record per env
   int32_t n;
   int32_t obs_dim;
+  int32_t snapshot_per_env;  // 0: one reset state for every env; 1: one per env (randomised start poses)
 };
 
 template <int CH>
@@ -71,8 +72,10 @@ __device__ __forceinline__ bool env_finite(const EnvState<float, CH> &s) {
 }
 
 template <int CH>
-__device__ __forceinline__ void load_snapshot(const ModelT<float> &M, const float *snap, EnvState<float, CH> &s) {
-  load_state<float, CH, float>(M, snap, 1, s);
+__device__ __forceinline__ void load_snapshot(const ModelT<float> &M, const Buffers &B, const int64_t env,
+                                              EnvState<float, CH> &s) {
+  if (B.snapshot_per_env) load_state<float, CH, float>(M, B.snapshot + env, B.n, s);
+  else load_state<float, CH, float>(M, B.snapshot, 1, s);
 }
 
 // warp-level reduction, one atomic per warp and counter
@@ -187,7 +190,7 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
 #pragma unroll
       for (int k = 0; k < CH; k++) yl[l][k] = y[(int64_t)(6 + l * CH + k) * B.n];
     finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
-    if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B.snapshot, s); nan = 1; }
+    if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B, env, s); nan = 1; }
   }
   if (B.diag) {
     // fold this step's per-env solver statistics into the running totals
@@ -230,7 +233,7 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
       __syncthreads();
     }
     if (live && done) {
-      load_snapshot<CH>(M, B.snapshot, s);
+      load_snapshot<CH>(M, B, env, s);
       for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
       float e[3];
       euler_from_quat(s.quat, e);
@@ -281,7 +284,8 @@ __global__ void reset_kernel(const Buffers B, const int state_dim, const uint8_t
   const int64_t env = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= B.n) return;
   if (mask && !mask[env]) return;
-  for (int f = 0; f < state_dim; f++) B.state[(int64_t)f * B.n + env] = B.snapshot[f];
+  for (int f = 0; f < state_dim; f++)
+    B.state[(int64_t)f * B.n + env] = B.snapshot_per_env ? B.snapshot[(int64_t)f * B.n + env] : B.snapshot[f];
   for (int t = 0; t < kMaxTermTerms; t++) B.counters[(int64_t)t * B.n + env] = 0;
   if (B.stats) { B.stats[env] = 0.f; B.stats[(int64_t)B.n + env] = 0.f; }
 }

@@ -206,6 +206,13 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
                    float *obs_host, float *reward_host, uint8_t *done_host,
                    void *stream);
 
+/* Layout of the snapshot buffer bound with solo_bind: per_env = 0 (default) one
+ * reset state float[state_dim] shared by every environment -- the reference's
+ * reset() is deterministic (solo8v2vanilla.py:104-143); per_env = 1 one reset state
+ * per environment, float[state_dim][n_envs], for start poses that differ per
+ * environment.  solo_reset, the in-kernel auto reset and the NaN
+ * guard all restore from it. */
+int solo_snapshot_layout(SoloHandle h, int32_t per_env);
 /* Diagnostics: per-step solver statistics of the last solo_step/solo_simulate
  * (sum over envs of contact points, PGS iterations run, NaN resets), written to
  * a caller device buffer int64[4] when bound (NULL to disable). */

@@ -280,3 +280,47 @@ def test_user_defined_plugins_run_unfused_and_match_the_fused_builtins():
     assert not bool(da.any()) and not bool(db.any())
     assert torch.equal(a.get_state(), b.get_state())                 # same physics either way
   a.close(); b.close()
+
+
+def test_per_env_start_poses_and_snapshots():
+  """SURVEY 8f N2 (start-pose part): robot_start_pos / robot_start_orientation_euler given
+  per environment.  The 500 settle steps run for the whole batch on the GPU, every env
+  keeps ITS OWN reset snapshot (solo_snapshot_layout), and the in-kernel auto reset
+  restores it.  Checked against the oracle's settle from the same poses."""
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  n, T = 48, 3
+  rng = np.random.RandomState(71)
+  pos = np.stack([rng.uniform(-1, 1, n), rng.uniform(-1, 1, n), rng.uniform(0.35, 0.6, n)], axis=1)
+  eul = np.stack([np.zeros(n), np.zeros(n), rng.uniform(-np.pi, np.pi, n)], axis=1)
+  cfg = Solo8VanillaConfig()
+  cfg.dt = 1.0 / 240.0
+  cfg.robot_start_pos = pos
+  cfg.robot_start_orientation_euler = eul
+  env = Solo8VanillaEnv(config=cfg, num_envs=n, device='cuda:0', auto_reset=True)
+  env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    env.reward_factory.register_reward(1, rewards.UprightReward(env.robot))
+  env.termination_factory.register_termination(termination.TimeBasedTermination(T))
+  env.reset()
+  start = env.get_state().clone()
+  got = start.double().cpu().numpy()
+  assert np.abs(got[:, 0:2] - pos[:, 0:2]).max() < 0.05          # every env settled where it was dropped
+  assert not torch.allclose(start[0], start[1])
+  orc = oracle(env._model, env._sim_config)
+  for i in (0, 7, 19):
+    want = orc.settle(START_TARGETS, pos=tuple(pos[i]), euler=tuple(eul[i]))
+    e = state_errors(got[i], want, env._model.ndof)
+    assert e['base_pos'] <= 5e-3 and e['q'] <= 5e-2, (i, e)
+  g = torch.Generator(device='cuda:0').manual_seed(72)
+  for k in range(1, T + 2):
+    act = (torch.rand((n, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    o, r, d, info = env.step(act)
+  assert bool(d.all())
+  assert torch.equal(env.get_state(), start)                      # each env back on its own snapshot
+  env.step(act)
+  env.reset(mask=torch.arange(n, device='cuda:0') % 2 == 0)       # masked reset restores per env too
+  st = env.get_state()
+  assert torch.equal(st[0::2], start[0::2]) and not torch.equal(st[1::2], start[1::2])
+  env.close()

@@ -22,6 +22,7 @@ for f, g in (('bench_4096.json', 'bench_4096'), ('bench_65536.json', 'bench_6553
   if os.path.exists(src):
     shutil.copy(src, os.path.join(PROF, '%s_%s%s' % (tag, g, os.path.splitext(f)[1])))
 traffic = {}
+insts = {}
 for k in kernels:
   rep = os.path.join(OUT, '%s_%s.ncu-rep' % (k, tag))
   if not os.path.exists(rep):
@@ -40,11 +41,12 @@ for k in kernels:
     u, v = d[name]
     return float(v.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
   traffic[k] = byt('dram__bytes_read.sum') + byt('dram__bytes_write.sum')
+  insts[k] = float(d['smsp__inst_executed.sum'][1].replace(',', ''))
   sub = {'setup_kernel': 'setup_kernel+ILi2E', 'solve_warp_kernel': 'solve_warp_kernel+ILi2ELb0', 'finish_kernel': 'finish_kernel+ILi2E',
          'solve_gram_kernel': 'solve_gram_kernel+ILi2ELb0'}.get(k, k)
   txt = subprocess.run([sys.executable, os.path.join(ROOT, 'tools', 'ncu_lines.py'), rep, sub, '40'], text=True,
                        capture_output=True).stdout
   open(os.path.join(PROF, '%s_%s_lines.txt' % (tag, k)), 'w').write(txt)
 json.dump({'envs': 4096, 'round': tag, 'how': 'ncu --set full --clock-control none, one launch inside bench.py (cold caches: ncu flushes between passes)',
-           'dram_bytes_per_launch': traffic}, open(os.path.join(PROF, 'traffic.json'), 'w'), indent=1)
+           'dram_bytes_per_launch': traffic, 'warp_instructions_per_launch': insts}, open(os.path.join(PROF, 'traffic.json'), 'w'), indent=1)
 print(traffic)
