@@ -222,9 +222,14 @@ class BatchedClient:
 
   def step_host(self, actions_np, scale, obs_np, reward_np, done_np):
     """Host buffers in, host buffers out (the reference's calling convention)."""
-    _lib.check(self.lib.solo_step_host(
-        self.handle, C.c_void_p(actions_np.ctypes.data), float(scale), C.c_void_p(obs_np.ctypes.data),
-        C.c_void_p(reward_np.ctypes.data), C.c_void_p(done_np.ctypes.data), self._stream()), self.handle)
+    key = (id(actions_np), id(obs_np), id(reward_np), id(done_np))
+    cached = getattr(self, '_host_ptrs', None)
+    if cached is None or cached[0] != key:
+      cached = (key, tuple(C.c_void_p(x.ctypes.data) for x in (actions_np, obs_np, reward_np, done_np)),
+                (actions_np, obs_np, reward_np, done_np))      # keeps the arrays (and their ids) alive
+      self._host_ptrs = cached
+    pa, po, pr, pd = cached[1]
+    _lib.check(self.lib.solo_step_host(self.handle, pa, float(scale), po, pr, pd, self._stream()), self.handle)
 
   def enable_debug(self, on=True):
     """Record per-step contact normal forces [n_cand, N] and applied motor

@@ -205,12 +205,17 @@ class Solo8VanillaEnv(Solo8BaseEnv):
                         obs=out[:n * d * 4].view(torch.float32).view(n, d),
                         rew=out[n * d * 4:n * d * 4 + n * 4].view(torch.float32),
                         done=out[n * d * 4 + n * 4:])
+      # numpy views of the pinned block, made once (the returned arrays alias it: they are
+      # overwritten by the next step_host, like the staging buffers of any vector env)
+      hh = self._host
+      hh['np'] = (hh['act'].numpy(), hh['obs'].numpy(), hh['rew'].numpy(), hh['done'].numpy())
+      hh['done_bool'] = hh['np'][3].view(np.bool_)
+      hh['info'] = {'labels': plan['labels']}
     h = self._host
-    a = h['act'].numpy()
+    a, o, r, dn = h['np']
     a[...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
-    c.step_host(a, self._scale(), h['obs'].numpy(), h['rew'].numpy(), h['done'].numpy())
-    return (h['obs'].numpy(), h['rew'].numpy(), h['done'].numpy().astype(bool),
-            {'labels': plan['labels']})
+    c.step_host(a, self._scale(), o, r, dn)
+    return o, r, h['done_bool'], h['info']
 
   # ---- reset ----------------------------------------------------------------------
   def reset(self, init_call: bool = False, mask=None):
