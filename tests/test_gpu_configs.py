@@ -324,3 +324,33 @@ def test_per_env_start_poses_and_snapshots():
   st = env.get_state()
   assert torch.equal(st[0::2], start[0::2]) and not torch.equal(st[1::2], start[1::2])
   env.close()
+
+
+@pytest.mark.parametrize('max_contacts,iters', [(8, 50), (64, 5), (1, 2)])
+def test_contact_cap_and_iteration_cap(max_contacts, iters):
+  """SoloConfig.max_contacts truncates the contact list in Bullet's order (by body, then by
+  support point) and solver_iterations caps the PGS sweeps: both must truncate exactly as
+  the oracle does (same contacts kept, same number of sweeps)."""
+  n = 96
+  c, model, config = make_client(n, dt=1.0 / 240.0, max_contacts=max_contacts, solver_iterations=iters)
+  full_cfg = model_and_config(dt=1.0 / 240.0)[2]
+  states = oracle_pool(model, full_cfg, n, 12, seed=81, targets=START_TARGETS)
+  rng = np.random.RandomState(82)
+  actions = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12))
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  st = c.solver_stats().cpu().numpy()
+  o = oracle(model, config)
+  want = np.zeros_like(states)
+  for i in range(n):
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i], d = o.step(s32, a32, diag=True)
+    assert d['n_contacts'] <= max_contacts and int(st[1, i]) == d['n_contacts']
+    assert int(st[0, i]) <= iters
+  assert st[1].max() == min(max_contacts, st[1].max()) and st[0].max() == iters
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL.items():
+    assert err[k] <= tol, (k, err)
+  c.disconnect()
