@@ -231,6 +231,18 @@ class BatchedClient:
     pa, po, pr, pd = cached[1]
     _lib.check(self.lib.solo_step_host(self.handle, pa, float(scale), po, pr, pd, self._stream()), self.handle)
 
+  def set_link_friction(self, friction):
+    """Per-env lateral friction of the non-base links ([N], None restores the model's
+    value for every env): changeDynamics(lateralFriction=...) per environment."""
+    if friction is None:
+      self._link_friction = None
+      _lib.check(self.lib.solo_bind_link_friction(self.handle, None), self.handle)
+      return
+    t = torch.as_tensor(np.asarray(friction, dtype=np.float32) if not torch.is_tensor(friction) else friction)
+    t = t.to(device=self.device, dtype=torch.float32).reshape(self.n) * float(self.config.plane_friction)
+    self._link_friction = t.contiguous()
+    _lib.check(self.lib.solo_bind_link_friction(self.handle, _ptr(self._link_friction)), self.handle)
+
   def enable_debug(self, on=True):
     """Record per-step contact normal forces [n_cand, N] and applied motor
     torques [ndof, N] (getContactPoints()[9] / getJointState()[3])."""

@@ -252,6 +252,12 @@ int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev) {
   return SOLO_OK;
 }
 
+int solo_bind_link_friction(SoloHandle h, const float *link_friction_dev) {
+  if (!h) return SOLO_EINVAL;
+  h->B.link_friction = link_friction_dev;
+  return SOLO_OK;
+}
+
 int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev) {
   if (!h) return SOLO_EINVAL;
   h->B.dbg_normal_force = normal_force_dev;

@@ -47,6 +47,7 @@ struct Buffers {
   unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, physics steps
   float *dbg_normal_force;   // [n_cand][n] or null
   float *dbg_motor_torque;   // [ndof][n] or null
+  const float *link_friction; // [n] or null: per-env friction of every non-base link x plane friction (solo_bind_link_friction)
   // solver scratch (caller-bound, solo_scratch_bytes)
   const float *cand_tab;     // [kMaxCand][kCandStride] support point xyz, friction, leg, depth
   float *yh;                 // [6 + kLegs * CH + 4][n]: solver output, then per-env solver statistics

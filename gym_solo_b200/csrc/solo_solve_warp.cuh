@@ -114,10 +114,12 @@ __device__ __forceinline__ float dense_gap(const float (&r)[N], const float (&y)
 // The owner lane of a promoted contact expands its three rows into entry `e`.
 template <int CH>
 __device__ __noinline__ void build_entry(float *e, const float *kin, const ConfigT<float> &C, const float margin,
-                                         const float *cand_tab, const int cand, const int contact, const float lam_n) {
+                                         const float *cand_tab, const int cand, const int contact, const float lam_n,
+                                         const float link_mu) {
   typedef RowLayout<CH> RL;
   typedef ActiveLayout<CH> AL;
-  const Cand k = load_cand(cand_tab, cand);
+  Cand k = load_cand(cand_tab, cand);
+  if (link_mu >= 0.f && k.leg >= 0) k.mu = link_mu;   // per-env friction of the non-base links
   float rows[3][RL::kRow];
   build_contact_rows<CH, 3>(kin, C, margin, k, cand, rows);
   store_dense<CH>(e, rows[0], k.leg, 2, AL::NW);
@@ -131,9 +133,9 @@ __device__ __noinline__ void build_entry(float *e, const float *kin, const Confi
 // Returns iterations; y = yh, mlam = scaled motor impulses, *n_active = entries of sm.ent.
 template <int CH, int NR>
 __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH> &sm, const float margin,
-                                          const float *cand_tab, const uint32_t motor_mask, const int nc,
-                                          const int lane, float (&y)[6 + kLegs * CH], float (&mlam)[kLegs * CH],
-                                          int *n_active) {
+                                          const float *cand_tab, const float link_mu, const uint32_t motor_mask,
+                                          const int nc, const int lane, float (&y)[6 + kLegs * CH],
+                                          float (&mlam)[kLegs * CH], int *n_active) {
   typedef RowLayout<CH> RL;
   typedef KinLayout<CH> KL;
   typedef ActiveLayout<CH> AL;
@@ -264,7 +266,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
               for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
             __syncwarp();
             // the owner lane builds the contact's three rows (the friction pair for the first time)
-            if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv);
+            if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv, link_mu);
             act |= MK::bit(v);
             n_act++;
             __syncwarp();
@@ -382,8 +384,9 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   float y[W], mlam[kLegs * CH];
   int it = 0, n_active = 0;
   if (motor_mask != 0 || nc > 0) {
-    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, motor_mask, nc, lane, y, mlam, &n_active);
-    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, motor_mask, nc, lane, y, mlam, &n_active);
+    const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
+    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, nc, lane, y, mlam, &n_active);
+    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, nc, lane, y, mlam, &n_active);
   } else {
 #pragma unroll
     for (int a = 0; a < W; a++) y[a] = 0.f;

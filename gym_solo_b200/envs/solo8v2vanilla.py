@@ -78,14 +78,19 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     self._blob = _abi.load_model_blob(cfg.urdf)
     # changeDynamics on joints 0..n-1 (solo8v2vanilla.py:157-163): every link but
     # the base gets config.lateral_friction; the base keeps its URDF value
-    self._model = _abi.make_model(self._blob, link_friction=cfg.lateral_friction)
+    # (a [num_envs] array of lateral frictions = one value per environment)
+    per_env_friction = np.ndim(cfg.lateral_friction) == 1
+    self._model = _abi.make_model(self._blob, link_friction=float(np.mean(cfg.lateral_friction)))
     self._sim_config = _abi.make_config(
         dt=cfg.dt, gravity=tuple(cfg.gravity), motor_torque_limit=cfg.motor_torque_limit,
         linear_damping=cfg.linear_damping, angular_damping=cfg.angular_damping,
         num_substeps=cfg.num_substeps, control_mode=_CONTROL[cfg.control_mode],
         max_contacts=cfg.max_contacts, solver_iterations=cfg.solver_iterations)
-    return bclient.BatchedClient(self._blob, self._model, self._sim_config, self.num_envs,
-                                 self.device)
+    client = bclient.BatchedClient(self._blob, self._model, self._sim_config, self.num_envs,
+                                   self.device)
+    if per_env_friction:
+      client.set_link_friction(cfg.lateral_friction)
+    return client
 
   def load_bodies(self):
     """solo8v2vanilla.py:145-172."""

@@ -217,6 +217,12 @@ int solo_snapshot_layout(SoloHandle h, int32_t per_env);
  * (sum over envs of contact points, PGS iterations run, NaN resets), written to
  * a caller device buffer int64[4] when bound (NULL to disable). */
 int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
+/* Per-environment lateral friction: float[n_envs] on the device,
+ * entry e = friction coefficient of every non-base link of environment e times
+ * the plane's (what changeDynamics(lateralFriction=...) sets for joints 0..n-1,
+ * solo8v2vanilla.py:157-163, combined as Bullet does with the plane's); the base
+ * keeps its model value.  NULL (default): the model's values for every env. */
+int solo_bind_link_friction(SoloHandle h, const float *link_friction_dev);
 /* Parity harness: per-step contact normal force per support point
  * (float[n_cand][n_envs], == getContactPoints()[9]) and applied motor torque per
  * dof (float[ndof][n_envs], == getJointState()[3]) of the last physics step.

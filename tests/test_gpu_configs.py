@@ -354,3 +354,39 @@ def test_contact_cap_and_iteration_cap(max_contacts, iters):
   for k, tol in TOL.items():
     assert err[k] <= tol, (k, err)
   c.disconnect()
+
+
+def test_per_env_link_friction():
+  """SURVEY 8f N2 (friction part): changeDynamics(lateralFriction=...) with one value per
+  environment (solo_bind_link_friction); each env against an oracle whose model carries
+  that env's friction."""
+  n = 96
+  c, model, config = make_client(n, dt=1.0 / 240.0)
+  blob = model_and_config(dt=1.0 / 240.0)[0]
+  states = oracle_pool(model, config, n, 12, seed=91, targets=START_TARGETS)
+  rng = np.random.RandomState(92)
+  actions = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12))
+  mus = rng.uniform(0.1, 1.5, n).astype(np.float32)
+  c.set_link_friction(mus)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  want = np.zeros_like(states)
+  base = np.zeros_like(states)
+  o0 = oracle(model, config)
+  for i in range(n):
+    oi = oracle(_abi.make_model(blob, link_friction=float(mus[i])), config)
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i] = oi.step(s32, a32)
+    base[i] = o0.step(s32, a32)
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL.items():
+    assert err[k] <= tol, (k, err)
+  assert state_errors(base, want, model.ndof)['qd'] > 0.05        # the friction values do matter here
+  c.set_link_friction(None)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  err = state_errors(c.get_state().double().cpu().numpy(), base, model.ndof)
+  assert err['qd'] <= TOL['qd'] and err['q'] <= TOL['q']
+  c.disconnect()
