@@ -108,6 +108,52 @@ class SoloProgram(C.Structure):
   ]
 
 
+class SoloCamera(C.Structure):
+  _fields_ = [
+      ('view', C.c_float * 16), ('proj', C.c_float * 16),
+      ('light_direction', C.c_float * 3), ('ambient', C.c_float), ('diffuse', C.c_float),
+      ('background', C.c_float * 3), ('plane_rgb_a', C.c_float * 3), ('plane_rgb_b', C.c_float * 3),
+      ('checker_size', C.c_float), ('width', C.c_int32), ('height', C.c_int32),
+  ]
+
+
+# render() shading defaults (ours: the reference leaves them to pybullet's renderer, which is
+# absent here -- DESIGN.md section 9): light towards (-5, -40, 200)/|.|, ambient 0.6, diffuse 0.35
+RENDER_DEFAULTS = dict(light_direction=(-5., -40., 200.), ambient=0.6, diffuse=0.35,
+                       background=(1., 1., 1.), plane_rgb_a=(1., 1., 1.), plane_rgb_b=(0.55, 0.65, 0.85),
+                       checker_size=0.5)
+
+
+def make_camera(view, proj, width, height, **shading):
+  opts = dict(RENDER_DEFAULTS)
+  for k, v in shading.items():
+    if k not in opts:
+      raise ValueError('unknown render option %r' % k)
+    opts[k] = v
+  if len(view) != 16 or len(proj) != 16:
+    raise ValueError('view and projection matrices are 16 floats, column-major')
+  cam = SoloCamera()
+  for i in range(16):
+    cam.view[i], cam.proj[i] = float(view[i]), float(proj[i])
+  for k in ('light_direction', 'background', 'plane_rgb_a', 'plane_rgb_b'):
+    for i in range(3):
+      getattr(cam, k)[i] = float(opts[k][i])
+  cam.ambient, cam.diffuse = float(opts['ambient']), float(opts['diffuse'])
+  cam.checker_size = float(opts['checker_size'])
+  cam.width, cam.height = int(width), int(height)
+  return cam, opts
+
+
+def load_visual(blob):
+  """The render() mesh compiled next to the model blob (compile_model.py `visual`):
+  dict(n_tri, tri_body, tri_verts [n_tri][9] body coordinates, tri_rgba)."""
+  path = os.path.join(MODELS_DIR, blob['name'] + '_visual.json')
+  if not os.path.exists(path):
+    raise ValueError('no compiled render mesh for model %r' % blob['name'])
+  with open(path) as f:
+    return json.load(f)
+
+
 MODELS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'assets')
 
 

@@ -14,7 +14,7 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, 'libsolo8_b200.so')
 SOURCES = [os.path.join(_PKG, 'csrc', f) for f in
            ('solo_abi.cu', 'solo_kernels.cuh', 'solo_core.h', 'solo_phases.h', 'solo_setup.h', 'solo_solve.h',
-            'solo_finish.h', 'solo_solve_warp.cuh', 'solo_contact.cuh', 'solo_convert.h')]
+            'solo_finish.h', 'solo_solve_warp.cuh', 'solo_contact.cuh', 'solo_convert.h', 'solo_render.cuh')]
 HEADER = os.path.join(_ROOT, 'include', 'solo8_b200.h')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
               '-std=c++17', '-shared', '-Xcompiler', '-fPIC']
@@ -69,6 +69,10 @@ EXPORTS = {
     'solo_block_size': (C.c_int, [C.c_void_p]),
     'solo_solver_lanes': (C.c_int, [C.c_void_p]),
     'solo_solver_stats': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    'solo_bind_mesh': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]),
+    'solo_render_scratch_bytes': (C.c_int64, [C.c_void_p, C.c_int32]),
+    'solo_render': (C.c_int, [C.c_void_p, C.POINTER(_abi.SoloCamera), C.c_int32, C.c_int32, C.c_void_p,
+                              C.c_void_p, C.c_void_p]),
 }
 
 

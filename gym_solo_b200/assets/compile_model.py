@@ -82,6 +82,10 @@ def parse_urdf(path):
                   [g('ixy'), g('iyy'), g('iyz')],
                   [g('ixz'), g('iyz'), g('izz')]])
     I = Rin @ I @ Rin.T          # inertia in link-frame axes
+    vis = l.find('visual')
+    rgba = [0.8, 0.8, 0.8, 1.0]
+    if vis is not None and vis.find('material') is not None and vis.find('material').find('color') is not None:
+      rgba = _floats(vis.find('material').find('color').get('rgba'), 4)
     col = l.find('collision')
     mesh, cxyz, cR = None, np.zeros(3), np.eye(3)
     if col is not None:
@@ -94,7 +98,7 @@ def parse_urdf(path):
     if c is not None and c.find('lateral_friction') is not None:
       mu = float(c.find('lateral_friction').get('value'))
     links[l.get('name')] = dict(name=l.get('name'), mass=mass, com=com, I=I,
-                                mesh=mesh, cxyz=cxyz, cR=cR, mu=mu)
+                                mesh=mesh, cxyz=cxyz, cR=cR, mu=mu, rgba=rgba)
   for j in root.findall('joint'):
     xyz, R = _origin(j)
     ax = j.find('axis')
@@ -145,6 +149,33 @@ def support_points(hv, kind):
   return np.array(pts)
 
 
+def fibonacci_dirs(n):
+  """n roughly uniform unit directions."""
+  k = np.arange(n) + 0.5
+  z = 1 - 2 * k / n
+  r = np.sqrt(1 - z * z)
+  th = math.pi * (1 + 5 ** 0.5) * k
+  return np.stack([r * np.cos(th), r * np.sin(th), z], 1)
+
+
+def visual_hull(hv, n_dirs):
+  """Triangles (outward, counter-clockwise) of the hull of the support points of
+  `hv` in n_dirs directions plus the six axis directions: a decimated convex
+  stand-in for the link mesh that render() rasterises."""
+  from scipy.spatial import ConvexHull
+  dirs = np.concatenate([fibonacci_dirs(n_dirs), np.eye(3), -np.eye(3)])
+  ext = np.maximum(hv.max(0) - hv.min(0), 1e-9)
+  pts = np.unique(hv[((hv / ext) @ dirs.T).argmax(0)], axis=0)
+  hull = ConvexHull(pts)
+  tris = []
+  for simplex, eq in zip(hull.simplices, hull.equations):
+    a, b, c = pts[simplex]
+    if np.cross(b - a, c - a) @ eq[:3] < 0:
+      b, c = c, b
+    tris.append(np.concatenate([a, b, c]))
+  return np.array(tris)
+
+
 def link_kind(name):
   n = name.lower()
   if 'foot' in n:
@@ -175,7 +206,11 @@ def principal_frame(I):
   return np.array([c[0] for c in cols]), R
 
 
-def compile_model(urdf_path, name=None, fallback_boxes=None):
+def compile_model(urdf_path, name=None, fallback_boxes=None, visual=None, visual_dirs=40):
+  """`visual`: optional dict that receives the render() mesh (tri_body, tri_verts
+  in body coordinates, tri_rgba): the decimated convex hull of every link's
+  collision mesh (the reference's URDFs use the same STL for <visual> and
+  <collision>), or the fallback box where the STL is absent."""
   links, joints, children, base = parse_urdf(urdf_path)
   mesh_dir = os.path.dirname(urdf_path)
   fallback_boxes = fallback_boxes or {}
@@ -263,10 +298,11 @@ def compile_model(urdf_path, name=None, fallback_boxes=None):
   # ---- collision support points ---------------------------------------------
   cand_body, cand_pos, cand_mu, cand_link = [], [], [], []
   hull_cache = {}
+  tri_body, tri_verts, tri_rgba = [], [], []
   for bi, body in enumerate(bodies):
     for l, p, R in body['parts']:
       L = links[l]
-      pts = None
+      pts, hv = None, None
       if L['mesh'] is not None:
         mp = os.path.join(mesh_dir, L['mesh'])
         if os.path.exists(mp):
@@ -274,13 +310,21 @@ def compile_model(urdf_path, name=None, fallback_boxes=None):
             from scipy.spatial import ConvexHull
             v = read_stl(mp)
             hull_cache[mp] = v[ConvexHull(v).vertices]
-          pts = support_points(hull_cache[mp], link_kind(l))
+          hv = hull_cache[mp]
+          pts = support_points(hv, link_kind(l))
       if pts is None and l in fallback_boxes:
         lo, hi = fallback_boxes[l]
         pts = np.array([[x, y, z] for x in (lo[0], hi[0]) for y in (lo[1], hi[1])
                         for z in (lo[2], hi[2])])
+        hv = pts
       if pts is None:
         continue
+      if visual is not None:
+        for t in visual_hull(hv, visual_dirs):
+          w = [p + R @ (L['cxyz'] + L['cR'] @ t[3 * k:3 * k + 3]) for k in range(3)]
+          tri_body.append(bi)
+          tri_verts.append(np.concatenate(w).round(6).tolist())
+          tri_rgba.append(L['rgba'])
       for q in pts:
         q_link = L['cxyz'] + L['cR'] @ q
         cand_body.append(bi)
@@ -307,6 +351,9 @@ def compile_model(urdf_path, name=None, fallback_boxes=None):
       n_cand=len(cand_body), cand_body=cand_body, cand_pos=cand_pos,
       cand_mu=cand_mu, cand_link=cand_link, collision_margin=0.001,
   )
+  if visual is not None:
+    visual.update(name=model['name'], source=model['source'], n_tri=len(tri_body),
+                  tri_body=tri_body, tri_verts=tri_verts, tri_rgba=tri_rgba)
   return model
 
 

@@ -24,6 +24,7 @@ import torch
 
 from gym_solo_b200 import _abi
 from gym_solo_b200 import _lib
+from gym_solo_b200 import camera
 
 ROBOT_ID = 1   # plane is body 0, robot body 1 (solo8_base_env.py:47, solo8v2vanilla.py:151)
 
@@ -73,6 +74,55 @@ class BatchedClient:
     self._program_token = None
     self._dbg = None
     self._staging = None
+    self._mesh = None
+    self._render_scratch = None
+
+  # ---- render (solo8_base_env.py:116-142) ---------------------------------------
+  def computeProjectionMatrixFOV(self, fov, aspect, nearVal, farVal):
+    return camera.compute_projection_matrix_fov(fov, aspect, nearVal, farVal)
+
+  def computeViewMatrixFromYawPitchRoll(self, cameraTargetPosition, distance, yaw, pitch, roll,
+                                        upAxisIndex):
+    return camera.compute_view_matrix_from_yaw_pitch_roll(cameraTargetPosition, distance, yaw, pitch,
+                                                          roll, upAxisIndex)
+
+  def bind_mesh(self, visual=None):
+    """Upload the render mesh (default: the one compiled next to the model blob)."""
+    v = visual if visual is not None else _abi.load_visual(self.blob)
+    dev = self.device
+    body = torch.tensor(v['tri_body'], dtype=torch.int32, device=dev).reshape(-1)
+    verts = torch.tensor(v['tri_verts'], dtype=torch.float32, device=dev).reshape(-1, 9).contiguous()
+    rgba = torch.tensor(v['tri_rgba'], dtype=torch.float32, device=dev).reshape(-1, 4).contiguous()
+    if not (body.numel() == verts.shape[0] == rgba.shape[0]):
+      raise ValueError('render mesh tables disagree in length')
+    if body.numel() and (int(body.min()) < 0 or int(body.max()) > self.ndof):
+      raise ValueError('render mesh refers to a body the model does not have')
+    _lib.check(self.lib.solo_bind_mesh(self.handle, _ptr(body), _ptr(verts), _ptr(rgba), int(body.numel())),
+               self.handle)
+    self._mesh = (body, verts, rgba)
+    self._render_scratch = None
+
+  def getCameraImage(self, width, height, viewMatrix, projectionMatrix, env_begin=0, env_count=1,
+                     out=None, **shading):
+    """pybullet.getCameraImage for environments [env_begin, env_begin + env_count):
+    returns (width, height, rgba) with rgba a uint8 device tensor
+    [env_count, height, width, 4].  Depth and segmentation are not produced."""
+    if self._mesh is None:
+      self.bind_mesh()
+    cam, _ = _abi.make_camera(viewMatrix, projectionMatrix, width, height, **shading)
+    need = int(self.lib.solo_render_scratch_bytes(self.handle, int(env_count)))
+    if need < 0:
+      raise ValueError('env_count must be >= 1')
+    if self._render_scratch is None or self._render_scratch.numel() < need:
+      self._render_scratch = torch.empty((need,), dtype=torch.uint8, device=self.device)
+    if out is None:
+      out = torch.empty((int(env_count), int(height), int(width), 4), dtype=torch.uint8, device=self.device)
+    elif (out.dtype != torch.uint8 or not out.is_contiguous() or out.device != self.device
+          or out.numel() != int(env_count) * int(height) * int(width) * 4):
+      raise ValueError('out must be a contiguous uint8 [env_count, height, width, 4] tensor on the device')
+    _lib.check(self.lib.solo_render(self.handle, C.byref(cam), int(env_begin), int(env_count), _ptr(out),
+                                    _ptr(self._render_scratch), self._stream()), self.handle)
+    return int(width), int(height), out
 
   # ---- lifetime ---------------------------------------------------------------
   def disconnect(self):

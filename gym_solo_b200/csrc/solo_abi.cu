@@ -1,6 +1,7 @@
 // solo_abi.cu -- the C-ABI of include/solo8_b200.h over the sm_100a kernels.
 // No torch types, no CPU fallback: without a CUDA device solo_create fails with
 // SOLO_ENOGPU and nothing else can be called.
+#include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -11,6 +12,7 @@
 #include "../../include/solo8_b200.h"
 #include "solo_convert.h"
 #include "solo_kernels.cuh"
+#include "solo_render.cuh"
 #include "solo_solve_warp.cuh"
 
 using namespace solo;
@@ -30,6 +32,10 @@ struct SoloHandle_ {
   float *st_actions, *st_obs, *st_reward;
   uint8_t *st_done;
   int64_t launches;
+  // render(): triangle mesh in body coordinates (device, caller-owned)
+  const int32_t *tri_body;
+  const float *tri_verts, *tri_rgba;
+  int32_t n_tri;
   // optional live per-phase timing (bench.py roofline): 4 events per physics step
   bool timing;
   std::vector<cudaEvent_t> ev;
@@ -108,6 +114,50 @@ static int opt_in_smem(SoloHandle h, F *kernel, size_t bytes) {
   return SOLO_OK;
 }
 
+// SoloCamera (column-major view / proj) -> the constants the render kernels read
+static std::string make_render_params(const SoloCamera &cam, RenderParams *out) {
+  RenderParams &R = *out;
+  memset(&R, 0, sizeof R);
+  auto V = [&](int r, int c) { return (double)cam.view[c * 4 + r]; };
+  auto P = [&](int r, int c) { return (double)cam.proj[c * 4 + r]; };
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) {
+      double a = 0;
+      for (int k = 0; k < 4; k++) a += P(r, k) * V(k, c);
+      R.vp[r * 4 + c] = (float)a;
+    }
+  const double xs = P(0, 0), ys = P(1, 1), A = P(2, 2), Bz = P(2, 3);
+  if (!(xs > 0) || !(ys > 0) || P(3, 2) != -1.0 || !(Bz < 0) || A == 1.0 || A == -1.0)
+    return "solo_render: proj is not a perspective projection (computeProjectionMatrixFOV)";
+  for (int i = 0; i < 3; i++) {
+    // view = [Rv | t]: eye = -Rv^T t; rows of Rv are right, up, -forward
+    R.eye[i] = (float)-(V(0, i) * V(0, 3) + V(1, i) * V(1, 3) + V(2, i) * V(2, 3));
+    R.ray_x[i] = (float)(V(0, i) / xs);
+    R.ray_y[i] = (float)(V(1, i) / ys);
+    R.ray_z[i] = (float)-V(2, i);
+  }
+  R.depth_a = (float)A;
+  R.depth_b = (float)Bz;
+  R.near_t = (float)(Bz / (A - 1.0));
+  R.far_t = (float)(Bz / (A + 1.0));
+  double l2 = 0;
+  for (int i = 0; i < 3; i++) l2 += (double)cam.light_direction[i] * cam.light_direction[i];
+  if (!(l2 > 0)) return "solo_render: light_direction is zero";
+  for (int i = 0; i < 3; i++) {
+    R.light[i] = (float)(cam.light_direction[i] / sqrt(l2));
+    R.sky[i] = cam.background[i];
+    R.plane_a[i] = cam.plane_rgb_a[i];
+    R.plane_b[i] = cam.plane_rgb_b[i];
+  }
+  R.ambient = cam.ambient;
+  R.diffuse = cam.diffuse;
+  if (!(cam.checker_size > 0)) return "solo_render: checker_size must be positive";
+  R.inv_checker = 1.f / cam.checker_size;
+  R.width = cam.width;
+  R.height = cam.height;
+  return "";
+}
+
 extern "C" {
 
 const char *solo_version(void) { return "solo8_b200 0.1 (sm_100a)"; }
@@ -147,6 +197,9 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->st_actions = h->st_obs = h->st_reward = nullptr;
   h->st_done = nullptr;
   h->launches = 0;
+  h->tri_body = nullptr;
+  h->tri_verts = h->tri_rgba = nullptr;
+  h->n_tri = 0;
   h->timing = false;
   h->ev_used = 0;
   h->phase_ms[0] = h->phase_ms[1] = h->phase_ms[2] = 0;
@@ -465,5 +518,64 @@ int solo_solver_stats(SoloHandle h, const float **stats_dev) {
 }
 
 int solo_solver_lanes(SoloHandle h) { return h ? 0 : SOLO_EINVAL; }   // one warp per environment
+
+// ---- render() ------------------------------------------------------------------------
+int solo_bind_mesh(SoloHandle h, const int32_t *tri_body_dev, const float *tri_verts_dev,
+                   const float *tri_rgba_dev, int32_t n_tri) {
+  if (!h) return SOLO_EINVAL;
+  if (n_tri < 0 || (n_tri > 0 && (!tri_body_dev || !tri_verts_dev || !tri_rgba_dev)))
+    return fail(h, SOLO_EINVAL, "solo_bind_mesh: null triangle table");
+  h->tri_body = tri_body_dev;
+  h->tri_verts = tri_verts_dev;
+  h->tri_rgba = tri_rgba_dev;
+  h->n_tri = n_tri;
+  return SOLO_OK;
+}
+
+static size_t render_recs_bytes(const SoloHandle h, int64_t env_count) {
+  return align256(sizeof(TriRec) * (size_t)(h->n_tri > 0 ? h->n_tri : 1) * (size_t)env_count);
+}
+
+int64_t solo_render_scratch_bytes(SoloHandle h, int32_t env_count) {
+  if (!h || env_count < 1) return SOLO_EINVAL;
+  return (int64_t)(render_recs_bytes(h, env_count) + align256(sizeof(int32_t) * 4 * (size_t)env_count));
+}
+
+int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t env_count, uint8_t *rgba_dev,
+                void *scratch_dev, void *stream) {
+  if (!h || !cam || !rgba_dev || !scratch_dev) return fail(h, SOLO_EINVAL, "null argument");
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  if (env_begin < 0 || env_count < 1 || (int64_t)env_begin + env_count > h->B.n)
+    return fail(h, SOLO_EINVAL, "solo_render: environment range out of bounds");
+  if (env_count > 65535) return fail(h, SOLO_EINVAL, "solo_render: at most 65535 environments per call");
+  if (cam->width < 1 || cam->height < 1 || cam->width > 16384 || cam->height > 16384)
+    return fail(h, SOLO_EINVAL, "solo_render: bad image size");
+  if (((uintptr_t)scratch_dev & 255) != 0 || ((uintptr_t)rgba_dev & 3) != 0)
+    return fail(h, SOLO_EINVAL, "solo_render: scratch must be 256-byte aligned, the image 4-byte aligned");
+  RenderParams R;
+  std::string msg = make_render_params(*cam, &R);
+  if (!msg.empty()) return fail(h, SOLO_EINVAL, msg);
+  R.n_tri = h->n_tri;
+  R.env_begin = env_begin;
+  R.env_count = env_count;
+  R.tiles_x = (cam->width + kTileW - 1) / kTileW;
+  const int tiles_y = (cam->height + kTileH - 1) / kTileH;
+  DeviceGuard g(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  TriRec *recs = (TriRec *)scratch_dev;
+  int32_t *bbox = (int32_t *)((char *)scratch_dev + render_recs_bytes(h, env_count));
+  cudaError_t e = cudaMemsetAsync(bbox, 0x7f, sizeof(int32_t) * 4 * (size_t)env_count, st);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemsetAsync");
+  if (h->n_tri > 0) {
+    const dim3 grid((h->n_tri + kProjectThreads - 1) / kProjectThreads, env_count);
+    render_project_kernel<<<grid, kProjectThreads, 0, st>>>(h->K.M, R, h->B.state, h->B.n, h->tri_body,
+                                                             h->tri_verts, h->tri_rgba, recs, bbox);
+    int rc = check_launch(h, "render_project_kernel");
+    if (rc) return rc;
+  }
+  const dim3 grid(R.tiles_x * tiles_y, env_count);
+  render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev);
+  return check_launch(h, "render_raster_kernel");
+}
 
 }  // extern "C"

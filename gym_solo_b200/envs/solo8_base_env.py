@@ -78,10 +78,31 @@ class Solo8BaseEnv(ABC):
   def observation_space(self) -> spaces.Space:
     return self.obs_factory.get_observation_space()
 
-  def render(self, mode='rgb_array'):
-    """solo8_base_env.py:116-142 rasterises through pybullet's getCameraImage
-    (TinyRenderer / OpenGL).  Not on the step path; SURVEY.md 8f row N4."""
-    raise NotImplementedError('render() is not part of the accelerated step path')
+  def render(self, mode='rgb_array', envs=None):
+    """solo8_base_env.py:116-142: the camera of `config` (render_fov, render_pos,
+    render_cam_distance, render_yaw / pitch / roll, near 0.01, far 100, Z up)
+    through computeProjectionMatrixFOV, computeViewMatrixFromYawPitchRoll and
+    getCameraImage.  The image comes from the library's CUDA rasteriser (no
+    graphics API): link hulls, flat shading, checkerboard ground plane.
+
+    envs=None renders environment 0 and returns the reference's (h, w, 4) uint8
+    array; envs=(begin, count) returns a uint8 device tensor [count, h, w, 4]."""
+    if mode != 'rgb_array':
+      raise ValueError('only the rgb_array render mode exists (no display on this box)')
+    proj_matrix = self.client.computeProjectionMatrixFOV(
+        self.config.render_fov, self.config.render_aspect, 0.01, 100)
+    view_matrix = self.client.computeViewMatrixFromYawPitchRoll(
+        self.config.render_pos, self.config.render_cam_distance,
+        self.config.render_yaw, self.config.render_pitch,
+        self.config.render_roll, 2)
+    begin, count = (0, 1) if envs is None else (int(envs[0]), int(envs[1]))
+    w, h, rgb = self.client.getCameraImage(
+        self.config.render_width, self.config.render_height, view_matrix,
+        proj_matrix, env_begin=begin, env_count=count)
+    if envs is None:
+      # 4 channels for RGBA
+      return np.reshape(rgb[0].cpu().numpy(), (h, w, 4))
+    return rgb
 
   def client_configuration(self):
     """Overridable hook (solo8_base_env.py:144-148)."""

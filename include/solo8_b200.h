@@ -142,6 +142,21 @@ typedef struct SoloProgram {
   SoloTermTerm term[SOLO_MAX_TERM_TERMS];
 } SoloProgram;
 
+/* Camera and shading of solo_render.  view / proj are the 16-float column-major
+ * matrices pybullet's computeViewMatrixFromYawPitchRoll / computeProjectionMatrixFOV
+ * return (gym_solo/envs/solo8_base_env.py:129-135); proj must be a centred
+ * perspective frustum.  Colours are linear 0..1. */
+typedef struct SoloCamera {
+  float view[16];
+  float proj[16];
+  float light_direction[3];   /* from the scene towards the light, any length */
+  float ambient, diffuse;     /* pixel = rgb * (ambient + diffuse * max(0, n.l)) */
+  float background[3];
+  float plane_rgb_a[3], plane_rgb_b[3];   /* checkerboard of the ground plane z = 0 */
+  float checker_size;         /* metres per cell */
+  int32_t width, height;
+} SoloCamera;
+
 typedef struct SoloHandle_ *SoloHandle;
 
 /* BulletClient(DIRECT) + setGravity + setPhysicsEngineParameter + loadURDF +
@@ -237,6 +252,19 @@ int solo_solver_stats(SoloHandle h, const float **stats_dev);
 /* Environments per warp of the solver kernel: always 0 = one WARP per
  * environment (kept for callers of the earlier lane-per-environment solver). */
 int solo_solver_lanes(SoloHandle h);
+/* render() -- gym_solo/envs/solo8_base_env.py:116-142 (getCameraImage).  The
+ * mesh is a triangle soup in BODY coordinates (body 0 = base inertial frame, body
+ * d + 1 = link of dof d), device pointers owned by the caller: tri_body
+ * int32[n_tri], tri_verts float[n_tri][9], tri_rgba float[n_tri][4].
+ * solo_render rasterises environments [env_begin, env_begin + env_count) at their
+ * current state into rgba_dev, uint8[env_count][height][width][4] (device), with two
+ * launches on `stream`; scratch_dev holds solo_render_scratch_bytes(h, env_count)
+ * bytes, 256-byte aligned.  No graphics API, no host round trip. */
+int solo_bind_mesh(SoloHandle h, const int32_t *tri_body_dev, const float *tri_verts_dev,
+                   const float *tri_rgba_dev, int32_t n_tri);
+int64_t solo_render_scratch_bytes(SoloHandle h, int32_t env_count);
+int solo_render(SoloHandle h, const SoloCamera *camera, int32_t env_begin, int32_t env_count,
+                uint8_t *rgba_dev, void *scratch_dev, void *stream);
 /* Live per-kernel timing (bench.py roofline): while enabled every physics step
  * records CUDA events on the launching stream around its three kernels;
  * solo_phase_times synchronises on them and returns the number of physics
