@@ -137,20 +137,22 @@ static std::string make_render_params(const SoloCamera &cam, RenderParams *out) 
     R.ray_z[i] = (float)-V(2, i);
   }
   R.depth_a = (float)A;
-  R.depth_b = (float)Bz;
+  R.plane_k = R.eye[2] != 0.f ? (float)(-Bz / (double)R.eye[2]) : 0.f;
   R.near_t = (float)(Bz / (A - 1.0));
   R.far_t = (float)(Bz / (A + 1.0));
+  R.ndc_sx = (float)(2.0 / cam.width);
+  R.ndc_sy = (float)(2.0 / cam.height);
   double l2 = 0;
   for (int i = 0; i < 3; i++) l2 += (double)cam.light_direction[i] * cam.light_direction[i];
   if (!(l2 > 0)) return "solo_render: light_direction is zero";
-  for (int i = 0; i < 3; i++) {
-    R.light[i] = (float)(cam.light_direction[i] / sqrt(l2));
-    R.sky[i] = cam.background[i];
-    R.plane_a[i] = cam.plane_rgb_a[i];
-    R.plane_b[i] = cam.plane_rgb_b[i];
-  }
+  for (int i = 0; i < 3; i++) R.light[i] = (float)(cam.light_direction[i] / sqrt(l2));
   R.ambient = cam.ambient;
   R.diffuse = cam.diffuse;
+  // the plane's normal is +z: one shade for the whole checkerboard
+  const float li = R.ambient + R.diffuse * fmaxf(0.f, R.light[2]);
+  R.sky_rgba = pack_rgba(cam.background[0], cam.background[1], cam.background[2]);
+  R.plane_rgba_a = pack_rgba(cam.plane_rgb_a[0] * li, cam.plane_rgb_a[1] * li, cam.plane_rgb_a[2] * li);
+  R.plane_rgba_b = pack_rgba(cam.plane_rgb_b[0] * li, cam.plane_rgb_b[1] * li, cam.plane_rgb_b[2] * li);
   if (!(cam.checker_size > 0)) return "solo_render: checker_size must be positive";
   R.inv_checker = 1.f / cam.checker_size;
   R.width = cam.width;
@@ -558,7 +560,7 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
   R.n_tri = h->n_tri;
   R.env_begin = env_begin;
   R.env_count = env_count;
-  R.tiles_x = (cam->width + kTileW - 1) / kTileW;
+  const int tiles_x = (cam->width + kTileW - 1) / kTileW;
   const int tiles_y = (cam->height + kTileH - 1) / kTileH;
   DeviceGuard g(h->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -573,7 +575,7 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
     int rc = check_launch(h, "render_project_kernel");
     if (rc) return rc;
   }
-  const dim3 grid(R.tiles_x * tiles_y, env_count);
+  const dim3 grid(tiles_x, tiles_y, env_count);
   render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev);
   return check_launch(h, "render_raster_kernel");
 }

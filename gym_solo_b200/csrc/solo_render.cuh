@@ -39,13 +39,15 @@ struct RenderParams {
   float ray_x[3];          // camera right / proj xScale
   float ray_y[3];          // camera up / proj yScale
   float ray_z[3];          // camera forward
-  float depth_a, depth_b;  // ndc z = -depth_a + depth_b / t   (t = distance along ray_z)
+  float depth_a;           // ground plane: ndc z = -depth_a + plane_k * ray.z
+  float plane_k;           //   (= -proj[2][3] / eye.z; t = -eye.z / ray.z is the distance along ray_z)
   float near_t, far_t;
+  float ndc_sx, ndc_sy;    // 2 / width, 2 / height
   float light[3];          // unit vector towards the light
   float ambient, diffuse;
-  float sky[3], plane_a[3], plane_b[3];
+  uint32_t sky_rgba, plane_rgba_a, plane_rgba_b;   // packed, the plane colours already shaded
   float inv_checker;
-  int32_t width, height, n_tri, env_begin, env_count, tiles_x;
+  int32_t width, height, n_tri, env_begin, env_count;
 };
 
 struct TriRec {
@@ -54,7 +56,7 @@ struct TriRec {
   float4 c;   // z2, 1 / area (0: culled), rgba8 bits, unused
 };
 
-__device__ __forceinline__ uint32_t pack_rgba(float r, float g, float b) {
+__host__ __device__ __forceinline__ uint32_t pack_rgba(float r, float g, float b) {
   const uint32_t R = (uint32_t)(fminf(fmaxf(r, 0.f), 1.f) * 255.f + 0.5f);
   const uint32_t G = (uint32_t)(fminf(fmaxf(g, 0.f), 1.f) * 255.f + 0.5f);
   const uint32_t B = (uint32_t)(fminf(fmaxf(b, 0.f), 1.f) * 255.f + 0.5f);
@@ -145,16 +147,16 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
                      const int32_t *__restrict__ bbox, uint32_t *__restrict__ out) {
   __shared__ float4 sa[kRasterThreads], sb[kRasterThreads], sc[kRasterThreads];
   __shared__ int warp_cnt[kRasterThreads / 32];
-  const int slot = blockIdx.y;
+  const int slot = blockIdx.z;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-  const int tile_x = blockIdx.x % R.tiles_x, tile_y = blockIdx.x / R.tiles_x;
+  const int tile_x = blockIdx.x, tile_y = blockIdx.y;
   const int px = tile_x * kTileW + lane, py = tile_y * kTileH + wid;
   const float fx = (float)px + 0.5f, fy = (float)py + 0.5f;
   const float tx0 = (float)(tile_x * kTileW), tx1 = tx0 + (float)kTileW;
   const float ty0 = (float)(tile_y * kTileH), ty1 = ty0 + (float)kTileH;
 
   float best = 1.f;                       // ndc depth of the far plane
-  uint32_t colour = pack_rgba(R.sky[0], R.sky[1], R.sky[2]);
+  uint32_t colour = R.sky_rgba;
 
   const int4 bb = *reinterpret_cast<const int4 *>(bbox + 4 * slot);
   const bool touched = (float)bb.x < tx1 && (float)(-bb.z) > tx0 && (float)bb.y < ty1 && (float)(-bb.w) > ty0;
@@ -204,20 +206,15 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
 
   // ground plane z = 0 (plane.urdf, solo8_base_env.py:47): analytic ray hit, checkerboard
   {
-    const float nx = 2.f * fx / (float)R.width - 1.f, ny = 1.f - 2.f * fy / (float)R.height;
+    const float nx = fx * R.ndc_sx - 1.f, ny = 1.f - fy * R.ndc_sy;
     const float rz = R.ray_z[2] + nx * R.ray_x[2] + ny * R.ray_y[2];
     const float tt = -R.eye[2] / rz;
-    if (rz != 0.f && tt > R.near_t && tt < R.far_t) {
-      const float z = -R.depth_a + R.depth_b / tt;
-      if (z < best) {
-        const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
-        const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
-        const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
-        const float *pc = (cell & 1) ? R.plane_b : R.plane_a;
-        const float li = R.ambient + R.diffuse * fmaxf(0.f, R.light[2]);
-        best = z;
-        colour = pack_rgba(pc[0] * li, pc[1] * li, pc[2] * li);
-      }
+    const float z = -R.depth_a + R.plane_k * rz;
+    if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best) {
+      const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
+      const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
+      const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
+      colour = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
     }
   }
   if (px < R.width && py < R.height)

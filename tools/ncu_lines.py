@@ -50,8 +50,9 @@ def sass_lines(kernel_sub):
 def main():
   rep, ksub = sys.argv[1], sys.argv[2]
   top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-  raw = subprocess.check_output(['ncu', '-i', rep, '--page', 'source', '--csv'], text=True,
-                                stderr=subprocess.DEVNULL)
+  # reports with several kernels: keep the rows of the one asked for
+  raw = subprocess.check_output(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name',
+                                 'regex:' + ksub.split('+')[0]], text=True, stderr=subprocess.DEVNULL)
   rows = list(csv.reader(io.StringIO(raw)))
   hi = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
   hdr = rows[hi]
