@@ -575,7 +575,9 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
     int rc = check_launch(h, "render_project_kernel");
     if (rc) return rc;
   }
-  const dim3 grid(tiles_x, tiles_y, env_count);
+  // one frame alone needs every block it can get; a batch of frames fills the GPU anyway
+  R.tiles_per_block = env_count >= 32 ? 4 : 1;
+  const dim3 grid(tiles_x, (tiles_y + R.tiles_per_block - 1) / R.tiles_per_block, env_count);
   render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev);
   return check_launch(h, "render_raster_kernel");
 }

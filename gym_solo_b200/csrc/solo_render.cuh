@@ -8,8 +8,8 @@
 //   render_project_kernel  one thread per (environment, triangle): body poses
 //                  by forward kinematics from the SoA state (thirteen threads of
 //                  the block, shared memory), vertices to pixel coordinates,
-//                  flat Lambert shade, back-face cull; one 48-byte TriRec per
-//                  triangle plus the robot's screen bounding box per environment.
+//                  flat Lambert shade, back-face cull; one 64-byte TriRec per
+//                  triangle (affine barycentric and depth equations) plus the robot's screen bounding box per environment.
 //   render_raster_kernel   one block per (32 x 8 pixel tile, environment): the
 //                  block culls the environment's triangles against its tile 256
 //                  at a time (ballot compaction into shared memory), every thread
@@ -17,7 +17,7 @@
 //                  analytic ground plane z = 0 (checkerboard); one coalesced
 //                  128-byte row of RGBA per warp.
 //
-// HBM traffic per frame: the 4 W H output bytes; the TriRec table (48 B x
+// HBM traffic per frame: the 4 W H output bytes; the TriRec table (64 B x
 // n_tri per environment) is written once and re-read from L2 by the tiles inside
 // the robot's bounding box only.
 #ifndef SOLO_RENDER_CUH_
@@ -48,13 +48,24 @@ struct RenderParams {
   uint32_t sky_rgba, plane_rgba_a, plane_rgba_b;   // packed, the plane colours already shaded
   float inv_checker;
   int32_t width, height, n_tri, env_begin, env_count;
+  int32_t tiles_per_block;   // vertically adjacent tiles walked by one raster block
 };
 
+// One projected triangle.  Barycentric coordinates and depth are affine in the
+// pixel position (x, y): lambda_i = e[i].x * x + e[i].y * y + e[i].z, ndc depth
+// z = e[0].w * x + e[1].w * y + e[2].w.
 struct TriRec {
-  float4 a;   // x0 y0 x1 y1   (pixel coordinates, y down)
-  float4 b;   // x2 y2 z0 z1   (z = ndc depth)
-  float4 c;   // z2, 1 / area (0: culled), rgba8 bits, unused
+  float4 e[3];
+  int32_t box_lo, box_hi;   // pixel bounding box: (x0 | y0 << 16), (x1 | y1 << 16), int16 each; x1, y1 exclusive
+  uint32_t rgba;
+  int32_t valid;            // 0: culled (behind the camera, back face, degenerate)
 };
+static_assert(sizeof(TriRec) == 64, "TriRec is four float4");
+
+__device__ __forceinline__ int32_t pack_box(float x, float y) {
+  const int xi = (int)fminf(fmaxf(x, -32768.f), 32767.f), yi = (int)fminf(fmaxf(y, -32768.f), 32767.f);
+  return (xi & 0xffff) | (yi << 16);
+}
 
 __host__ __device__ __forceinline__ uint32_t pack_rgba(float r, float g, float b) {
   const uint32_t R = (uint32_t)(fminf(fmaxf(r, 0.f), 1.f) * 255.f + 0.5f);
@@ -120,19 +131,34 @@ render_project_kernel(const __grid_constant__ ModelT<float> M, const __grid_cons
   float area = (sx[1] - sx[0]) * (sy[2] - sy[0]) - (sx[2] - sx[0]) * (sy[1] - sy[0]);
   ok = ok && area < -1e-12f;
   TriRec rec;
-  rec.a = make_float4(sx[0], sy[0], sx[2], sy[2]);      // v1 <-> v2: positive area for the rasteriser
-  rec.b = make_float4(sx[1], sy[1], sz[0], sz[2]);
-  rec.c = make_float4(sz[1], 0.f, 0.f, 0.f);
+  rec.e[0] = rec.e[1] = rec.e[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+  rec.box_lo = rec.box_hi = 0;
+  rec.rgba = 0;
+  rec.valid = 0;
   if (ok) {
     V3<float> nrm = cross(w[1] - w[0], w[2] - w[0]);
     nrm = nrm * m_rsqrt(dot(nrm, nrm) + 1e-30f);
     const float li = R.ambient + R.diffuse * fmaxf(0.f, nrm.x * R.light[0] + nrm.y * R.light[1] + nrm.z * R.light[2]);
-    rec.c.y = -1.f / area;
-    rec.c.z = __uint_as_float(pack_rgba(tri_rgba[tri * 4 + 0] * li, tri_rgba[tri * 4 + 1] * li,
-                                        tri_rgba[tri * 4 + 2] * li));
-    int32_t *bb = bbox + 4 * slot;
+    rec.rgba = pack_rgba(tri_rgba[tri * 4 + 0] * li, tri_rgba[tri * 4 + 1] * li, tri_rgba[tri * 4 + 2] * li);
+    rec.valid = 1;
+    // v1 <-> v2: positive area for the rasteriser; edge i is opposite vertex i
+    const float X[3] = {sx[0], sx[2], sx[1]}, Y[3] = {sy[0], sy[2], sy[1]}, Z[3] = {sz[0], sz[2], sz[1]};
+    const float inv = -1.f / area;
+    float za = 0.f, zb = 0.f, zc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const int a = (i + 1) % 3, b = (i + 2) % 3;
+      const float A = -(Y[b] - Y[a]) * inv, B = (X[b] - X[a]) * inv;
+      const float C = -(A * X[a] + B * Y[a]);
+      rec.e[i].x = A; rec.e[i].y = B; rec.e[i].z = C;
+      za += A * Z[i]; zb += B * Z[i]; zc += C * Z[i];
+    }
+    rec.e[0].w = za; rec.e[1].w = zb; rec.e[2].w = zc;
     const float x0 = fminf(sx[0], fminf(sx[1], sx[2])), x1 = fmaxf(sx[0], fmaxf(sx[1], sx[2]));
     const float y0 = fminf(sy[0], fminf(sy[1], sy[2])), y1 = fmaxf(sy[0], fmaxf(sy[1], sy[2]));
+    rec.box_lo = pack_box(floorf(x0), floorf(y0));
+    rec.box_hi = pack_box(ceilf(x1), ceilf(y1));
+    int32_t *bb = bbox + 4 * slot;
     const float lim = 1e6f;
     atomicMin(bb + 0, (int)floorf(fmaxf(x0, -lim)));
     atomicMin(bb + 1, (int)floorf(fmaxf(y0, -lim)));
@@ -145,80 +171,88 @@ render_project_kernel(const __grid_constant__ ModelT<float> M, const __grid_cons
 __global__ void __launch_bounds__(kRasterThreads)
 render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__restrict__ recs,
                      const int32_t *__restrict__ bbox, uint32_t *__restrict__ out) {
-  __shared__ float4 sa[kRasterThreads], sb[kRasterThreads], sc[kRasterThreads];
+  __shared__ float4 se[3][kRasterThreads];
+  __shared__ uint32_t s_rgba[kRasterThreads];
   __shared__ int warp_cnt[kRasterThreads / 32];
   const int slot = blockIdx.z;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-  const int tile_x = blockIdx.x, tile_y = blockIdx.y;
-  const int px = tile_x * kTileW + lane, py = tile_y * kTileH + wid;
-  const float fx = (float)px + 0.5f, fy = (float)py + 0.5f;
-  const float tx0 = (float)(tile_x * kTileW), tx1 = tx0 + (float)kTileW;
-  const float ty0 = (float)(tile_y * kTileH), ty1 = ty0 + (float)kTileH;
-
-  float best = 1.f;                       // ndc depth of the far plane
-  uint32_t colour = R.sky_rgba;
-
+  const int tile_x = blockIdx.x;
+  const int px = tile_x * kTileW + lane;
+  const float fx = (float)px + 0.5f;
+  const int tx0 = tile_x * kTileW, tx1 = tx0 + kTileW;
   const int4 bb = *reinterpret_cast<const int4 *>(bbox + 4 * slot);
-  const bool touched = (float)bb.x < tx1 && (float)(-bb.z) > tx0 && (float)bb.y < ty1 && (float)(-bb.w) > ty0;
-  if (touched) {
-    const TriRec *mine = recs + (int64_t)slot * R.n_tri;
-    for (int base = 0; base < R.n_tri; base += kRasterThreads) {
-      const int idx = base + t;
-      TriRec rec;
-      bool keep = false;
-      if (idx < R.n_tri) {
-        rec = mine[idx];
-        if (rec.c.y != 0.f) {
-          const float x0 = fminf(rec.a.x, fminf(rec.a.z, rec.b.x)), x1 = fmaxf(rec.a.x, fmaxf(rec.a.z, rec.b.x));
-          const float y0 = fminf(rec.a.y, fminf(rec.a.w, rec.b.y)), y1 = fmaxf(rec.a.y, fmaxf(rec.a.w, rec.b.y));
-          keep = x0 < tx1 && x1 > tx0 && y0 < ty1 && y1 > ty0;
-        }
-      }
-      const unsigned m = __ballot_sync(0xffffffffu, keep);
-      if (lane == 0) warp_cnt[wid] = __popc(m);
-      __syncthreads();
-      int off = 0, total = 0;
-#pragma unroll
-      for (int k = 0; k < kRasterThreads / 32; k++) {
-        const int c = warp_cnt[k];
-        off += k < wid ? c : 0;
-        total += c;
-      }
-      if (keep) {
-        const int p = off + __popc(m & ((1u << lane) - 1u));   // triangle order is kept
-        sa[p] = rec.a; sb[p] = rec.b; sc[p] = rec.c;
-      }
-      __syncthreads();
-      for (int k = 0; k < total; k++) {
-        const float4 a = sa[k], b = sb[k], c = sc[k];
-        // edge functions of (v0, v1, v2) = (a.xy, a.zw, b.xy), positive inside
-        const float w0 = (b.x - a.z) * (fy - a.w) - (b.y - a.w) * (fx - a.z);
-        const float w1 = (a.x - b.x) * (fy - b.y) - (a.y - b.y) * (fx - b.x);
-        const float w2 = (a.z - a.x) * (fy - a.y) - (a.w - a.y) * (fx - a.x);
-        if (w0 >= 0.f && w1 >= 0.f && w2 >= 0.f) {
-          const float z = (w0 * b.z + w1 * b.w + w2 * c.x) * c.y;
-          if (z < best && z >= -1.f) { best = z; colour = __float_as_uint(c.z); }
-        }
-      }
-      __syncthreads();
-    }
-  }
+  const TriRec *mine = recs + (int64_t)slot * R.n_tri;
+  const int4 *meta0 = reinterpret_cast<const int4 *>(&mine[t < R.n_tri ? t : 0].box_lo);
 
-  // ground plane z = 0 (plane.urdf, solo8_base_env.py:47): analytic ray hit, checkerboard
-  {
-    const float nx = fx * R.ndc_sx - 1.f, ny = 1.f - fy * R.ndc_sy;
-    const float rz = R.ray_z[2] + nx * R.ray_x[2] + ny * R.ray_y[2];
-    const float tt = -R.eye[2] / rz;
-    const float z = -R.depth_a + R.plane_k * rz;
-    if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best) {
-      const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
-      const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
-      const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
-      colour = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
+  // several vertically adjacent tiles per block when there are many environments: the short
+  // sky / plane tiles amortise the block launch
+  for (int sub = 0; sub < R.tiles_per_block; sub++) {
+    const int tile_y = blockIdx.y * R.tiles_per_block + sub;
+    const int ty0 = tile_y * kTileH, ty1 = ty0 + kTileH;
+    if (ty0 >= R.height) break;
+    const int py = ty0 + wid;
+    const float fy = (float)py + 0.5f;
+
+    float best = 1.f;                       // ndc depth of the far plane
+    uint32_t colour = R.sky_rgba;
+
+    const bool touched = bb.x < tx1 && -bb.z > tx0 && bb.y < ty1 && -bb.w > ty0;
+    if (touched) {
+      int4 m_next = *meta0;
+      for (int base = 0; base < R.n_tri; base += kRasterThreads) {
+        const int idx = base + t;
+        const int4 m = m_next;
+        if (idx + kRasterThreads < R.n_tri)     // next chunk's bounding boxes fly during this chunk's pixels
+          m_next = *reinterpret_cast<const int4 *>(&mine[idx + kRasterThreads].box_lo);
+        const int x0 = (int)(short)(m.x & 0xffff), y0 = m.x >> 16, x1 = (int)(short)(m.y & 0xffff), y1 = m.y >> 16;
+        const bool keep = idx < R.n_tri && m.w != 0 && x0 < tx1 && x1 > tx0 && y0 < ty1 && y1 > ty0;
+        const unsigned mask = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_cnt[wid] = __popc(mask);
+        __syncthreads();
+        int off = 0, total = 0;
+#pragma unroll
+        for (int k = 0; k < kRasterThreads / 32; k++) {
+          const int c = warp_cnt[k];
+          off += k < wid ? c : 0;
+          total += c;
+        }
+        if (keep) {
+          const int p = off + __popc(mask & ((1u << lane) - 1u));   // triangle order is kept
+          const float4 *e = mine[idx].e;
+          se[0][p] = e[0]; se[1][p] = e[1]; se[2][p] = e[2];
+          s_rgba[p] = (uint32_t)m.z;
+        }
+        __syncthreads();
+        for (int k = 0; k < total; k++) {
+          const float4 e0 = se[0][k], e1 = se[1][k], e2 = se[2][k];
+          const float l0 = fmaf(e0.x, fx, fmaf(e0.y, fy, e0.z));
+          const float l1 = fmaf(e1.x, fx, fmaf(e1.y, fy, e1.z));
+          const float l2 = fmaf(e2.x, fx, fmaf(e2.y, fy, e2.z));
+          if (fminf(l0, fminf(l1, l2)) >= 0.f) {
+            const float z = fmaf(e0.w, fx, fmaf(e1.w, fy, e2.w));
+            if (z < best && z >= -1.f) { best = z; colour = s_rgba[k]; }
+          }
+        }
+        __syncthreads();
+      }
     }
+
+    // ground plane z = 0 (plane.urdf, solo8_base_env.py:47): analytic ray hit, checkerboard
+    {
+      const float nx = fx * R.ndc_sx - 1.f, ny = 1.f - fy * R.ndc_sy;
+      const float rz = R.ray_z[2] + nx * R.ray_x[2] + ny * R.ray_y[2];
+      const float tt = -R.eye[2] / rz;
+      const float z = -R.depth_a + R.plane_k * rz;
+      if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best) {
+        const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
+        const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
+        const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
+        colour = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
+      }
+    }
+    if (px < R.width && py < R.height)
+      out[((int64_t)slot * R.height + py) * R.width + px] = colour;
   }
-  if (px < R.width && py < R.height)
-    out[((int64_t)slot * R.height + py) * R.width + px] = colour;
 }
 
 }  // namespace solo
