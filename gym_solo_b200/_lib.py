@@ -53,6 +53,7 @@ EXPORTS = {
     'solo_snapshot_layout': (C.c_int, [C.c_void_p, C.c_int32]),
     'solo_bind_diag': (C.c_int, [C.c_void_p, C.c_void_p]),
     'solo_bind_link_friction': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'solo_bind_base_mass_scale': (C.c_int, [C.c_void_p, C.c_void_p]),
     'solo_bind_debug': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     'solo_bind_staging': (C.c_int, [C.c_void_p] * 5),
     'solo_simulate': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),

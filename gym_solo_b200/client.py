@@ -76,6 +76,8 @@ class BatchedClient:
     self._staging = None
     self._mesh = None
     self._render_scratch = None
+    self._link_friction = None
+    self._base_mass_scale = None
 
   # ---- render (solo8_base_env.py:116-142) ---------------------------------------
   def computeProjectionMatrixFOV(self, fov, aspect, nearVal, farVal):
@@ -193,12 +195,17 @@ class BatchedClient:
     cfg = _abi.SoloConfig.from_buffer_copy(self.config)
     cfg.control_mode = _abi.CONTROL_POSITION
     cfg.num_substeps = 1
-    if np.ndim(pos) == 2 or np.ndim(euler) == 2:
-      # start poses that differ per environment: the settle runs for the
-      # whole batch, one snapshot per env
+    if (np.ndim(pos) == 2 or np.ndim(euler) == 2 or self._link_friction is not None
+        or self._base_mass_scale is not None):
+      # start poses, friction or payload that differ per environment: the
+      # settle runs for the whole batch, one snapshot per env
       pos_n = np.broadcast_to(np.asarray(pos, dtype=np.float64), (self.n, 3))
       eul_n = np.broadcast_to(np.asarray(euler, dtype=np.float64), (self.n, 3))
       full = BatchedClient(self.blob, self.model, cfg, self.n, self.device)
+      if self._link_friction is not None:
+        _lib.check(self.lib.solo_bind_link_friction(full.handle, _ptr(self._link_friction)), full.handle)
+      if self._base_mass_scale is not None:
+        _lib.check(self.lib.solo_bind_base_mass_scale(full.handle, _ptr(self._base_mass_scale)), full.handle)
       full.set_state(np.stack([full.initial_state(pos_n[i], eul_n[i]) for i in range(self.n)]))
       a = torch.tensor(np.asarray(start_targets_api, dtype=np.float32), device=self.device)
       full.simulate(a, n_steps=n_steps, broadcast=True)
@@ -292,6 +299,20 @@ class BatchedClient:
     t = t.to(device=self.device, dtype=torch.float32).reshape(self.n) * float(self.config.plane_friction)
     self._link_friction = t.contiguous()
     _lib.check(self.lib.solo_bind_link_friction(self.handle, _ptr(self._link_friction)), self.handle)
+
+  def set_base_mass_scale(self, scale):
+    """Per-env factor on the base body's mass and inertia ([N] > 0; None restores the
+    model's base for every env)."""
+    if scale is None:
+      self._base_mass_scale = None
+      _lib.check(self.lib.solo_bind_base_mass_scale(self.handle, None), self.handle)
+      return
+    t = torch.as_tensor(np.asarray(scale, dtype=np.float32) if not torch.is_tensor(scale) else scale)
+    t = t.to(device=self.device, dtype=torch.float32).reshape(self.n).contiguous()
+    if not bool((t > 0).all()):
+      raise ValueError('base mass scales must be positive')
+    self._base_mass_scale = t
+    _lib.check(self.lib.solo_bind_base_mass_scale(self.handle, _ptr(t)), self.handle)
 
   def enable_debug(self, on=True):
     """Record per-step contact normal forces [n_cand, N] and applied motor

@@ -313,6 +313,12 @@ int solo_bind_link_friction(SoloHandle h, const float *link_friction_dev) {
   return SOLO_OK;
 }
 
+int solo_bind_base_mass_scale(SoloHandle h, const float *scale_dev) {
+  if (!h) return SOLO_EINVAL;
+  h->B.base_mass_scale = scale_dev;
+  return SOLO_OK;
+}
+
 int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev) {
   if (!h) return SOLO_EINVAL;
   h->B.dbg_normal_force = normal_force_dev;

@@ -47,6 +47,7 @@ struct Buffers {
   unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, physics steps
   float *dbg_normal_force;   // [n_cand][n] or null
   float *dbg_motor_torque;   // [ndof][n] or null
+  const float *base_mass_scale; // [n] or null: per-env factor on the base body's mass and inertia (solo_bind_base_mass_scale)
   const float *link_friction; // [n] or null: per-env friction of every non-base link x plane friction (solo_bind_link_friction)
   // solver scratch (caller-bound, solo_scratch_bytes)
   const float *cand_tab;     // [kMaxCand][kCandStride] support point xyz, friction, leg, depth
@@ -155,7 +156,8 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
   EnvState<float, CH> s;
   load_state<float, CH, float>(M, B.state + env, B.n, s);
   float *kin = B.kin + env * KL::kSize;
-  setup_step<float, CH, false>(M, K.C, s, cmd, nullptr, kin + KL::kMotor, RL::kRow, B.fac + env, B.n, kin);
+  setup_step<float, CH, false>(M, K.C, s, cmd, nullptr, kin + KL::kMotor, RL::kRow, B.fac + env, B.n, kin,
+                               B.base_mass_scale ? B.base_mass_scale[env] : 1.f);
 }
 
 // ---------------------------------------------------------------------------------

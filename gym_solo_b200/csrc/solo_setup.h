@@ -30,7 +30,7 @@ namespace solo {
 template <typename T, int CH, bool CONTACTS = true>
 SOLO_HD RowHeader setup_step(const ModelT<T> &M, const ConfigT<T> &C, const EnvState<T, CH> &s,
                              const T (&cmd)[kLegs][CH], const T *cand_tab, T *rows, int64_t slot_stride, T *fac,
-                             int64_t fac_stride, T *kin = nullptr) {
+                             int64_t fac_stride, T *kin = nullptr, T base_scale = T(1)) {
   typedef RowLayout<CH> RL;
   typedef FactorLayout<CH> FL;
   const T dt = C.dt;
@@ -44,13 +44,17 @@ SOLO_HD RowHeader setup_step(const ModelT<T> &M, const ConfigT<T> &C, const EnvS
 
   // totals about c0: bias force/moment and composite inertia (mass, m*r, I_O)
   V3<T> Ftot, Ntot;
-  T mtot = M.mass[0];
+  // base_scale: per-environment factor on the base body's mass and inertia (solo_bind_base_mass_scale)
+  const T mass0 = M.mass[0] * base_scale;
+  T mtot = mass0;
   V3<T> htot = mk(T(0), T(0), T(0));
   S3<T> Itot = rotate_inertia(R0, M.inertia[0]);
+  Itot.xx *= base_scale; Itot.xy *= base_scale; Itot.xz *= base_scale;
+  Itot.yy *= base_scale; Itot.yz *= base_scale; Itot.zz *= base_scale;
   {
     T vn = m_sqrt(dot(vc0, vc0)), wn = m_sqrt(dot(w0, w0));
     V3<T> Iw = mul(Itot, w0);
-    V3<T> fext = grav * M.mass[0] - vc0 * (M.mass[0] * (C.lin_damp + C.lin_damp * vn));
+    V3<T> fext = grav * mass0 - vc0 * (mass0 * (C.lin_damp + C.lin_damp * vn));
     V3<T> next = Iw * (-(C.ang_damp + C.ang_damp * wn));
     Ftot = mk(T(0), T(0), T(0)) - fext;
     Ntot = cross(w0, Iw) - next;

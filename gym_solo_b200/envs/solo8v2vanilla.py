@@ -90,6 +90,9 @@ class Solo8VanillaEnv(Solo8BaseEnv):
                                    self.device)
     if per_env_friction:
       client.set_link_friction(cfg.lateral_friction)
+    # config.base_mass_scale ([num_envs], optional; not a reference field): per-env payload
+    if getattr(cfg, 'base_mass_scale', None) is not None:
+      client.set_base_mass_scale(cfg.base_mass_scale)
     return client
 
   def load_bodies(self):

@@ -238,6 +238,11 @@ int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev);
  * solo8v2vanilla.py:157-163, combined as Bullet does with the plane's); the base
  * keeps its model value.  NULL (default): the model's values for every env. */
 int solo_bind_link_friction(SoloHandle h, const float *link_friction_dev);
+/* Per-environment payload (domain randomisation): scale_dev[n_envs]
+ * (device, caller-owned, must stay alive) multiplies the BASE body's mass and
+ * inertia tensor in environment e; NULL restores the model's values.  The
+ * reference has one robot (changeDynamics(mass=...) would be its call). */
+int solo_bind_base_mass_scale(SoloHandle h, const float *scale_dev);
 /* Parity harness: per-step contact normal force per support point
  * (float[n_cand][n_envs], == getContactPoints()[9]) and applied motor torque per
  * dof (float[ndof][n_envs], == getJointState()[3]) of the last physics step.

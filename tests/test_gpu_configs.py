@@ -390,3 +390,79 @@ def test_per_env_link_friction():
   err = state_errors(c.get_state().double().cpu().numpy(), base, model.ndof)
   assert err['qd'] <= TOL['qd'] and err['q'] <= TOL['q']
   c.disconnect()
+
+
+def test_per_env_base_mass_scale():
+  """SURVEY 8f N2 (mass part): one payload factor per environment on the base body's mass
+  and inertia (solo_bind_base_mass_scale); each env against an oracle whose model carries
+  that env's base."""
+  n = 96
+  c, model, config = make_client(n, dt=1.0 / 240.0)
+  blob = model_and_config(dt=1.0 / 240.0)[0]
+  states = oracle_pool(model, config, n, 12, seed=101, targets=START_TARGETS)
+  rng = np.random.RandomState(102)
+  actions = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12))
+  scales = rng.uniform(0.6, 2.5, n).astype(np.float32)
+  c.set_base_mass_scale(scales)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  want = np.zeros_like(states)
+  base = np.zeros_like(states)
+  o0 = oracle(model, config)
+  for i in range(n):
+    mi = _abi.make_model(blob, link_friction=0.5)
+    mi.body_mass[0] *= float(scales[i])
+    for k in range(9):
+      mi.body_inertia[0][k] *= float(scales[i])
+    oi = oracle(mi, config)
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    a32 = actions[i].astype(np.float32).astype(np.float64)
+    want[i] = oi.step(s32, a32)
+    base[i] = o0.step(s32, a32)
+  err = state_errors(got, want, model.ndof)
+  for k, tol in TOL.items():
+    assert err[k] <= tol, (k, err)
+  assert state_errors(base, want, model.ndof)['base_lin'] > 0.01     # the payload does matter here
+  with pytest.raises(ValueError):
+    c.set_base_mass_scale(np.zeros(n))
+  c.set_base_mass_scale(None)
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  err = state_errors(c.get_state().double().cpu().numpy(), base, model.ndof)
+  assert err['qd'] <= TOL['qd'] and err['q'] <= TOL['q']
+  c.disconnect()
+
+
+def test_env_reset_settles_each_randomised_robot():
+  """reset() with a per-env payload: the 500 settle steps run per environment and every env
+  keeps its own snapshot.  The start pose folds the legs, so the robot comes to rest on its
+  torso: heavier robots press (a few 1e-8 m) deeper into the contact slop, never shallower;
+  env 0 (scale 1) equals the unrandomised settle."""
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  n = 8
+  cfg = Solo8VanillaConfig()
+  cfg.dt = 1.0 / 240.0
+  cfg.base_mass_scale = np.linspace(1.0, 3.0, n)
+  env = Solo8VanillaEnv(config=cfg, num_envs=n, device='cuda:0')
+  env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    env.reward_factory.register_reward(1, rewards.UprightReward(env.robot))
+  env.termination_factory.register_termination(termination.PerpetualTermination())
+  env.reset()
+  z = env.get_state()[:, 2].cpu().numpy()
+  ref_cfg = Solo8VanillaConfig()
+  ref_cfg.dt = 1.0 / 240.0
+  ref = Solo8VanillaEnv(config=ref_cfg, num_envs=2, device='cuda:0')
+  ref.obs_factory.register_observation(obs.TorsoIMU(ref.robot))
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    ref.reward_factory.register_reward(1, rewards.UprightReward(ref.robot))
+  ref.termination_factory.register_termination(termination.PerpetualTermination())
+  ref.reset()
+  z_ref = float(ref.get_state()[0, 2])
+  assert abs(z[0] - z_ref) < 1e-5
+  assert env.client.snapshot.dim() == 2 and tuple(env.client.snapshot.shape)[1] == n
+  assert np.all(np.isfinite(z)) and np.all(np.diff(z) <= 1e-9) and z[-1] < z[0]
