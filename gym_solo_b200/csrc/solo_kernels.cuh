@@ -108,9 +108,23 @@ __device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t
   const int ps = pad_stride(k);
   const int total = n_valid * k;
   const float *src = g + env0 * k;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int r = i / k, c = i - r * k;
-    sm[r * ps + c] = src[i];
+  // loads in batches of kU per thread so that their latencies overlap
+  constexpr int kU = 6;
+  for (int i = threadIdx.x; i < total; i += kU * blockDim.x) {
+    float v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int ii = i + u * blockDim.x;
+      v[u] = ii < total ? __ldg(src + ii) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int ii = i + u * blockDim.x;
+      if (ii < total) {
+        const int r = ii / k, c = ii - r * k;
+        sm[r * ps + c] = v[u];
+      }
+    }
   }
   __syncthreads();
 }
@@ -144,6 +158,9 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
   const bool live = env < B.n;
   const int n_api = M.n_api;
 
+  // the state loads go out first: they fly while the action tile is gathered
+  EnvState<float, CH> s;
+  if (live) load_state<float, CH, float>(M, B.state + env, B.n, s);
   float cmd[kLegs][CH];
   if (broadcast) {
     load_command<float, CH, float>(M, actions, action_scale, cmd);
@@ -153,8 +170,6 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
     if (live) load_command<float, CH, float>(M, smem + threadIdx.x * pad_stride(n_api), action_scale, cmd);
   }
   if (!live) return;
-  EnvState<float, CH> s;
-  load_state<float, CH, float>(M, B.state + env, B.n, s);
   float *kin = B.kin + env * KL::kSize;
   setup_step<float, CH, false>(M, K.C, s, cmd, nullptr, kin + KL::kMotor, RL::kRow, B.fac + env, B.n, kin,
                                B.base_mass_scale ? B.base_mass_scale[env] : 1.f);
