@@ -269,8 +269,8 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
     h->B.fac = (float *)(base + L.fac);
     h->B.kin = (float *)(base + L.kin);
     // support-point table of the solver warp: xyz, friction, leg (-1 base), depth in the chain
-    static float tab[kCandStride * kMaxCand];
-    memset(tab, 0, sizeof tab);
+    std::vector<float> tab_v(kCandStride * kMaxCand, 0.f);   // per call: handles may be bound from several threads
+    float *tab = tab_v.data();
     const ModelT<float> &M = h->K.M;
     for (int body = 0; body <= M.ndof; body++) {
       int leg = -1, depth = 0;
@@ -284,7 +284,7 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
       }
     }
     DeviceGuard g(h->device);
-    cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof tab, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof(float) * tab_v.size(), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return cuda_fail(h, e, "upload of the support-point table");
   }
   h->B.state = state_dev;
