@@ -345,7 +345,7 @@ def main():
     e2e_value = world * n * e2e_steps / (max(e2e_ms, e2e_wall_ms) * 1e-3)
     peak, peak_kind = hbm_peak()
     step_ms = float(per_step_ms.mean())
-    names = ['setup_kernel', 'solve_warp_kernel', 'finish_kernel']
+    names = ['setup_legpar_kernel', 'solve_warp_kernel', 'finish_kernel']
     dom = int(np.argmax(phase_ms))
     launch_ms = phase_ms[dom]
     achieved = BYTES_PER_ENV_STEP * n / (launch_ms * 1e-3) / 1e9

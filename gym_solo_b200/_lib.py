@@ -14,7 +14,7 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, 'libsolo8_b200.so')
 SOURCES = [os.path.join(_PKG, 'csrc', f) for f in
            ('solo_abi.cu', 'solo_kernels.cuh', 'solo_core.h', 'solo_phases.h', 'solo_setup.h', 'solo_solve.h',
-            'solo_finish.h', 'solo_solve_warp.cuh', 'solo_contact.cuh', 'solo_convert.h', 'solo_render.cuh')]
+            'solo_finish.h', 'solo_solve_warp.cuh', 'solo_contact.cuh', 'solo_convert.h', 'solo_render.cuh', 'solo_setup_legpar.cuh')]
 HEADER = os.path.join(_ROOT, 'include', 'solo8_b200.h')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
               '-std=c++17', '-shared', '-Xcompiler', '-fPIC']

@@ -2,12 +2,16 @@
 //
 // One env.step = three launches on the caller's stream (solo_phases.h):
 //
-//   setup_kernel   one thread per environment: the part of a step whose size
-//                  does not depend on the pose.  Reads the action tile and the
-//                  SoA state, runs kinematics, bias forces, the mass-matrix
-//                  factorisation and the motor rows; writes the factors [k][env]
-//                  for finish_kernel and one contiguous KinLayout record per
-//                  environment for the solver warp.
+//   setup_legpar_kernel (solo_setup_legpar.cuh)  one lane per (environment, leg):
+//                  the part of a step whose size does not depend on the pose.
+//                  Reads the action tile and the SoA state, runs kinematics, bias
+//                  forces, the mass-matrix factorisation and the motor rows (legs in
+//                  parallel, their sums by xor-shuffle, the 6 x 6 base part on all
+//                  four lanes); writes the factors [k][env] for finish_kernel and one
+//                  contiguous KinLayout record per environment for the solver warp.
+//                  setup_kernel below is the one-thread-per-environment form of the
+//                  same phase (setup_step of solo_setup.h, shared with the host
+//                  tests), kept for A/B runs (SOLO_SETUP=serial).
 //   solve_warp_kernel (solo_solve_warp.cuh)  one warp per environment: contact
 //                  detection and contact rows one contact per lane, then the
 //                  data-dependent part: projected Gauss-Seidel, a serial chain

@@ -4,7 +4,7 @@
 TAG=${1:-r1x}
 O=gpurun_out
 mkdir -p $O
-K='setup_kernel|solve_warp_kernel|finish_kernel'
+K='setup_legpar_kernel|solve_warp_kernel|finish_kernel'
 python -m pytest tests -m gpu -q 2>&1 | tail -3 > $O/pytest_gpu.txt; cat $O/pytest_gpu.txt
 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
 python bench.py --steps 300 --warmup 20 > $O/bench_4096.json 2> $O/bench_4096.err; cat $O/bench_4096.json
@@ -15,7 +15,7 @@ python tools/bench_render.py 4096 1 200 > $O/render_1.json 2>/dev/null; cat $O/r
 # profiler passes last: nothing printed under ncu is a bench value
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$K" --launch-skip 1509 -c 120 --csv \
   --log-file $O/launches_c.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
-for k in setup_kernel solve_warp_kernel finish_kernel; do
+for k in setup_legpar_kernel solve_warp_kernel finish_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$k --launch-skip 520 -c 1 -f -o $O/${k}_$TAG \
     python bench.py --steps 10 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
 done

@@ -3,7 +3,7 @@ round tag: bench lines, the ncu launch list, key rows of the `ncu --set full`
 captures (one csv per kernel), per-source-line stall tables, and
 profiles/traffic.json (dram bytes per launch, read by bench.py's roofline.traffic).
 
-  python tools/save_profiles.py r1c setup_kernel solve_warp_kernel finish_kernel
+  python tools/save_profiles.py r1f setup_legpar_kernel solve_warp_kernel finish_kernel
 """
 import csv, io, json, os, shutil, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -42,7 +42,7 @@ for k in kernels:
     return float(v.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
   traffic[k] = byt('dram__bytes_read.sum') + byt('dram__bytes_write.sum')
   insts[k] = float(d['smsp__inst_executed.sum'][1].replace(',', ''))
-  sub = {'setup_kernel': 'setup_kernel+ILi2E', 'solve_warp_kernel': 'solve_warp_kernel+ILi2ELb0', 'finish_kernel': 'finish_kernel+ILi2E',
+  sub = {'setup_kernel': 'setup_kernel+ILi2E', 'setup_legpar_kernel': 'setup_legpar_kernel+ILi2E', 'solve_warp_kernel': 'solve_warp_kernel+ILi2ELb0', 'finish_kernel': 'finish_kernel+ILi2E',
          'solve_gram_kernel': 'solve_gram_kernel+ILi2ELb0'}.get(k, k)
   txt = subprocess.run([sys.executable, os.path.join(ROOT, 'tools', 'ncu_lines.py'), rep, sub, '40'], text=True,
                        capture_output=True).stdout
