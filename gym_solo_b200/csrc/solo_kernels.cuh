@@ -106,12 +106,16 @@ __device__ __forceinline__ void diag_add(unsigned long long *diag, int contacts,
 // smem holds blockDim.x * k floats; rows are padded to an odd stride to keep the
 // per-thread row accesses conflict free.
 __device__ __forceinline__ int pad_stride(int k) { return k | 1; }
+// i / k for the flat index of a [rows <= 128][k <= 128] tile without an integer division:
+// (i + 1/2) / k is at least 1 / (2 k) away from every integer, far more than its float32 error
+__device__ __forceinline__ int tile_row(int i, float inv_k) { return (int)(((float)i + 0.5f) * inv_k); }
 
 __device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t env0, int n_valid, int k,
                                             float *sm) {
   const int ps = pad_stride(k);
   const int total = n_valid * k;
   const float *src = g + env0 * k;
+  const float inv_k = 1.f / (float)k;
   // loads in batches of kU per thread so that their latencies overlap
   constexpr int kU = 6;
   for (int i = threadIdx.x; i < total; i += kU * blockDim.x) {
@@ -125,7 +129,7 @@ __device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t
     for (int u = 0; u < kU; u++) {
       const int ii = i + u * blockDim.x;
       if (ii < total) {
-        const int r = ii / k, c = ii - r * k;
+        const int r = tile_row(ii, inv_k), c = ii - r * k;
         sm[r * ps + c] = v[u];
       }
     }
@@ -137,9 +141,10 @@ __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0
   const int ps = pad_stride(k);
   const int total = n_valid * k;
   float *dst = g + env0 * k;
+  const float inv_k = 1.f / (float)k;
   __syncthreads();
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int r = i / k, c = i - r * k;
+    const int r = tile_row(i, inv_k), c = i - r * k;
     dst[i] = sm[r * ps + c];
   }
 }
