@@ -313,6 +313,8 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         load_row(e + AL::kFA, fa);
         load_row(e + AL::kFB, fb);
         const float4 l4 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
+        // no normal impulse and no friction impulse: the disc has radius 0, the update is exactly a no-op
+        if (l4.x == 0.f && l4.y == 0.f && l4.z == 0.f) continue;
         float sa = dense_gap<W>(fa, y, l4.y), sb = dense_gap<W>(fb, y, l4.z);
         const float limit = fa[W + 3] * l4.x;                  // mu * lambda_n, true units
         const float ta = sa * fa[W + 2], tb = sb * fb[W + 2];  // true units
