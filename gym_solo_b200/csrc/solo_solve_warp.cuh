@@ -179,6 +179,9 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   float budget = 0.f;
   int n_act = 0;
   int it = 0;
+#ifdef SOLO_IDLE_PROBE
+  int probe_visits = 0, probe_idle = 0;   // probe build: how many promoted-contact visits found the contact idle
+#endif
   for (; it < C.iters;) {
     float res = 0.f;
     // ---- motor rows (btMultiBodyJointMotor), direction alternates with parity ----
@@ -314,6 +317,10 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         load_row(e + AL::kFB, fb);
         const float4 l4 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
         // no normal impulse and no friction impulse: the disc has radius 0, the update is exactly a no-op
+#ifdef SOLO_IDLE_PROBE
+        probe_visits++;
+        if (l4.x == 0.f && l4.y == 0.f && l4.z == 0.f) probe_idle++;
+#endif
         if (l4.x == 0.f && l4.y == 0.f && l4.z == 0.f) continue;
         float sa = dense_gap<W>(fa, y, l4.y), sb = dense_gap<W>(fb, y, l4.z);
         const float limit = fa[W + 3] * l4.x;                  // mu * lambda_n, true units
@@ -334,6 +341,9 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
     if (res <= C.res_thr) break;
   }
   *n_active = n_act;
+#ifdef SOLO_IDLE_PROBE
+  *n_active = n_act + 1000 * (probe_visits > 0 ? (100 * probe_idle) / probe_visits : 0);
+#endif
   return it;
 }
 
