@@ -122,8 +122,14 @@ class BatchedClient:
     elif (out.dtype != torch.uint8 or not out.is_contiguous() or out.device != self.device
           or out.numel() != int(env_count) * int(height) * int(width) * 4):
       raise ValueError('out must be a contiguous uint8 [env_count, height, width, 4] tensor on the device')
-    _lib.check(self.lib.solo_render(self.handle, C.byref(cam), int(env_begin), int(env_count), _ptr(out),
-                                    _ptr(self._render_scratch), self._stream()), self.handle)
+    # one call takes at most 65535 environments (grid z): larger ranges go in chunks
+    frame = int(height) * int(width) * 4
+    flat = out.view(-1)
+    for b in range(0, int(env_count), 65535):
+      cnt = min(65535, int(env_count) - b)
+      _lib.check(self.lib.solo_render(self.handle, C.byref(cam), int(env_begin) + b, cnt,
+                                      C.c_void_p(flat.data_ptr() + b * frame), _ptr(self._render_scratch),
+                                      self._stream()), self.handle)
     return int(width), int(height), out
 
   # ---- lifetime ---------------------------------------------------------------
