@@ -312,7 +312,10 @@ def main():
 
   # ---- end-to-end arm: host buffers through solo_step_host -----------------------------
   rng = np.random.RandomState(4321 + rank)
-  host_actions = [rng.uniform(-two_pi, two_pi, (n, 12)).astype(np.float32) for _ in range(16)]
+  # the step's inputs live in page-locked host memory (the contract's H2D source); step_host copies
+  # them to the device from there
+  host_actions = [torch.from_numpy(rng.uniform(-two_pi, two_pi, (n, 12)).astype(np.float32)).pin_memory()
+                  for _ in range(16)]
   for k in range(min(args.warmup, 5)):
     env.step_host(host_actions[k % 16])
   barrier()
@@ -371,7 +374,7 @@ def main():
                      'note': 'path is FP32-issue/latency bound, not HBM bound (SURVEY.md 8d)'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * n * 12 * 4,
                 'd2h_bytes_per_step': world * n * (21 * 4 + 4 + 1), 'steps': e2e_steps,
-                'api': 'Solo8VanillaEnv.step_host -> solo_step_host (pinned host buffers)',
+                'api': 'Solo8VanillaEnv.step_host(pinned float32 CPU tensor) -> solo_step_host: H2D actions, step, one D2H of obs|reward|done, stream sync; results read on the host',
                 'checksum': checksum},
         'gpu_launches': int(launches),
         'clocks': sampler.summary(),

@@ -283,7 +283,7 @@ class BatchedClient:
                      self._staging_out[n * obs_dim * 4 + n * 4:])
     _lib.check(self.lib.solo_bind_staging(self.handle, *[_ptr(t) for t in self._staging]), self.handle)
 
-  def step_host(self, actions_np, scale, obs_np, reward_np, done_np):
+  def step_host(self, actions_np, scale, obs_np, reward_np, done_np, actions_ptr=None):
     """Host buffers in, host buffers out (the reference's calling convention)."""
     key = (id(actions_np), id(obs_np), id(reward_np), id(done_np))
     cached = getattr(self, '_host_ptrs', None)
@@ -292,6 +292,8 @@ class BatchedClient:
                 (actions_np, obs_np, reward_np, done_np))      # keeps the arrays (and their ids) alive
       self._host_ptrs = cached
     pa, po, pr, pd = cached[1]
+    if actions_ptr is not None:
+      pa = C.c_void_p(actions_ptr)     # the caller's own pinned buffer: no staging copy
     _lib.check(self.lib.solo_step_host(self.handle, pa, float(scale), po, pr, pd, self._stream()), self.handle)
 
   def set_link_friction(self, friction):

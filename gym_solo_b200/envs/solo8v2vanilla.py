@@ -197,7 +197,9 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     """The reference's calling convention -- numpy in, numpy out -- through the
     C-ABI's host entry (solo_step_host): H2D of the actions, the fused step,
     D2H of observations / reward / done, and a stream synchronise.  Needs every
-    registered plug-in to be a built-in."""
+    registered plug-in to be a built-in.  `action`: a numpy array (staged through a pinned
+    buffer) or a pinned float32 CPU tensor (no staging copy).  The returned arrays alias
+    pinned staging memory and are overwritten by the next call."""
     plan = self._build_plan()
     if plan is None:
       raise ValueError('step_host needs built-in observations, rewards and terminations')
@@ -221,8 +223,14 @@ class Solo8VanillaEnv(Solo8BaseEnv):
       hh['info'] = {'labels': plan['labels']}
     h = self._host
     a, o, r, dn = h['np']
-    a[...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
-    c.step_host(a, self._scale(), o, r, dn)
+    if (torch.is_tensor(action) and action.device.type == 'cpu' and action.dtype == torch.float32
+        and action.is_contiguous() and action.numel() == c.n * c.n_api and action.is_pinned()):
+      # actions already in page-locked host memory (torch.empty(...).pin_memory()): copied to the
+      # device straight from there
+      c.step_host(a, self._scale(), o, r, dn, actions_ptr=action.data_ptr())
+    else:
+      a[...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
+      c.step_host(a, self._scale(), o, r, dn)
     return o, r, h['done_bool'], h['info']
 
   # ---- reset ----------------------------------------------------------------------

@@ -206,6 +206,14 @@ def test_step_host_matches_device_step():
     assert np.array_equal(o1.cpu().numpy(), o2)
     assert np.array_equal(r1.cpu().numpy(), r2)
     assert np.array_equal(d1.cpu().numpy(), d2)
+  # a pinned float32 CPU tensor goes to the device without the staging copy: same results
+  for _ in range(3):
+    act = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12)).astype(np.float32)
+    o1, r1, d1, _ = a_env.step(torch.tensor(act, device='cuda:0'))
+    o2, r2, d2, _ = b_env.step_host(torch.from_numpy(act).pin_memory())
+    assert np.array_equal(o1.cpu().numpy(), o2)
+    assert np.array_equal(r1.cpu().numpy(), r2)
+    assert np.array_equal(d1.cpu().numpy(), d2)
   a_env.close(); b_env.close()
 
 
