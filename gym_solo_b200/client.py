@@ -29,6 +29,7 @@ from gym_solo_b200 import camera
 ROBOT_ID = 1   # plane is body 0, robot body 1 (solo8_base_env.py:47, solo8v2vanilla.py:151)
 
 _SNAPSHOT_CACHE = {}
+_RAW_STREAM = getattr(torch._C, '_cuda_getCurrentRawStream', None)
 
 
 def _ptr(t):
@@ -145,6 +146,10 @@ class BatchedClient:
       pass
 
   def _stream(self):
+    # torch's current stream on this device; the raw getter skips building a Stream object
+    raw = _RAW_STREAM
+    if raw is not None:
+      return C.c_void_p(raw(self.index))
     return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
   # ---- program ----------------------------------------------------------------
