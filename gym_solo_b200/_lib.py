@@ -73,7 +73,7 @@ EXPORTS = {
     'solo_bind_mesh': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]),
     'solo_render_scratch_bytes': (C.c_int64, [C.c_void_p, C.c_int32]),
     'solo_render': (C.c_int, [C.c_void_p, C.POINTER(_abi.SoloCamera), C.c_int32, C.c_int32, C.c_void_p,
-                              C.c_void_p, C.c_void_p]),
+                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 

@@ -106,32 +106,38 @@ class BatchedClient:
     self._render_scratch = None
 
   def getCameraImage(self, width, height, viewMatrix, projectionMatrix, env_begin=0, env_count=1,
-                     out=None, **shading):
-    """pybullet.getCameraImage for environments [env_begin, env_begin + env_count):
-    returns (width, height, rgba) with rgba a uint8 device tensor
-    [env_count, height, width, 4].  Depth and segmentation are not produced."""
+                     out=None, depth=True, segmentation=True, **shading):
+    """pybullet.getCameraImage for environments [env_begin, env_begin + env_count): returns
+    pybullet's five values (width, height, rgba, depth, segmentation) as device tensors --
+    rgba uint8 [env_count, height, width, 4]; depth float32 [env_count, height, width], the
+    OpenGL depth buffer in [0, 1]; segmentation int32 (plane 0, robot 1, nothing -1).
+    depth=False / segmentation=False skip that image (None in its place)."""
     if self._mesh is None:
       self.bind_mesh()
     cam, _ = _abi.make_camera(viewMatrix, projectionMatrix, width, height, **shading)
-    need = int(self.lib.solo_render_scratch_bytes(self.handle, int(env_count)))
+    cnt_all, hh, ww = int(env_count), int(height), int(width)
+    need = int(self.lib.solo_render_scratch_bytes(self.handle, cnt_all))
     if need < 0:
       raise ValueError('env_count must be >= 1')
     if self._render_scratch is None or self._render_scratch.numel() < need:
       self._render_scratch = torch.empty((need,), dtype=torch.uint8, device=self.device)
     if out is None:
-      out = torch.empty((int(env_count), int(height), int(width), 4), dtype=torch.uint8, device=self.device)
+      out = torch.empty((cnt_all, hh, ww, 4), dtype=torch.uint8, device=self.device)
     elif (out.dtype != torch.uint8 or not out.is_contiguous() or out.device != self.device
-          or out.numel() != int(env_count) * int(height) * int(width) * 4):
+          or out.numel() != cnt_all * hh * ww * 4):
       raise ValueError('out must be a contiguous uint8 [env_count, height, width, 4] tensor on the device')
+    dep = torch.empty((cnt_all, hh, ww), dtype=torch.float32, device=self.device) if depth else None
+    seg = torch.empty((cnt_all, hh, ww), dtype=torch.int32, device=self.device) if segmentation else None
     # one call takes at most 65535 environments (grid z): larger ranges go in chunks
-    frame = int(height) * int(width) * 4
-    flat = out.view(-1)
-    for b in range(0, int(env_count), 65535):
-      cnt = min(65535, int(env_count) - b)
-      _lib.check(self.lib.solo_render(self.handle, C.byref(cam), int(env_begin) + b, cnt,
-                                      C.c_void_p(flat.data_ptr() + b * frame), _ptr(self._render_scratch),
-                                      self._stream()), self.handle)
-    return int(width), int(height), out
+    pix = hh * ww
+    for b in range(0, cnt_all, 65535):
+      cnt = min(65535, cnt_all - b)
+      _lib.check(self.lib.solo_render(
+          self.handle, C.byref(cam), int(env_begin) + b, cnt, C.c_void_p(out.data_ptr() + b * pix * 4),
+          C.c_void_p(dep.data_ptr() + b * pix * 4) if dep is not None else C.c_void_p(0),
+          C.c_void_p(seg.data_ptr() + b * pix * 4) if seg is not None else C.c_void_p(0),
+          _ptr(self._render_scratch), self._stream()), self.handle)
+    return ww, hh, out, dep, seg
 
   # ---- lifetime ---------------------------------------------------------------
   def disconnect(self):

@@ -564,7 +564,7 @@ int64_t solo_render_scratch_bytes(SoloHandle h, int32_t env_count) {
 }
 
 int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t env_count, uint8_t *rgba_dev,
-                void *scratch_dev, void *stream) {
+                float *depth_dev, int32_t *seg_dev, void *scratch_dev, void *stream) {
   if (!h || !cam || !rgba_dev || !scratch_dev) return fail(h, SOLO_EINVAL, "null argument");
   if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
   if (env_begin < 0 || env_count < 1 || (int64_t)env_begin + env_count > h->B.n)
@@ -598,7 +598,7 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
   // one frame alone needs every block it can get; a batch of frames fills the GPU anyway
   R.tiles_per_block = env_count >= 32 ? 4 : 1;
   const dim3 grid(tiles_x, (tiles_y + R.tiles_per_block - 1) / R.tiles_per_block, env_count);
-  render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev);
+  render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
   return check_launch(h, "render_raster_kernel");
 }
 

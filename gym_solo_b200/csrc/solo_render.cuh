@@ -170,7 +170,8 @@ render_project_kernel(const __grid_constant__ ModelT<float> M, const __grid_cons
 
 __global__ void __launch_bounds__(kRasterThreads)
 render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__restrict__ recs,
-                     const int32_t *__restrict__ bbox, uint32_t *__restrict__ out) {
+                     const int32_t *__restrict__ bbox, uint32_t *__restrict__ out, float *__restrict__ depth_out,
+                     int32_t *__restrict__ seg_out) {
   __shared__ float4 se[3][kRasterThreads];
   __shared__ uint32_t s_rgba[kRasterThreads];
   __shared__ int warp_cnt[kRasterThreads / 32];
@@ -238,20 +239,30 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
     }
 
     // ground plane z = 0 (plane.urdf, solo8_base_env.py:47): analytic ray hit, checkerboard
+    const bool on_robot = best < 1.f;   // a triangle won so far
+    bool on_plane = false;
     {
       const float nx = fx * R.ndc_sx - 1.f, ny = 1.f - fy * R.ndc_sy;
       const float rz = R.ray_z[2] + nx * R.ray_x[2] + ny * R.ray_y[2];
       const float tt = -R.eye[2] / rz;
       const float z = -R.depth_a + R.plane_k * rz;
       if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best) {
+        best = z;
+        on_plane = true;
         const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
         const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
         const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
         colour = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
       }
     }
-    if (px < R.width && py < R.height)
-      out[((int64_t)slot * R.height + py) * R.width + px] = colour;
+    if (px < R.width && py < R.height) {
+      const int64_t pix = ((int64_t)slot * R.height + py) * R.width + px;
+      out[pix] = colour;
+      // getCameraImage's other two images: OpenGL depth in [0, 1] (1 = far plane / nothing hit) and
+      // the body id (plane 0, robot 1, nothing -1)
+      if (depth_out) depth_out[pix] = 0.5f * best + 0.5f;
+      if (seg_out) seg_out[pix] = on_plane ? 0 : (on_robot ? 1 : -1);
+    }
   }
 }
 

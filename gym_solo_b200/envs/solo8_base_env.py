@@ -96,9 +96,9 @@ class Solo8BaseEnv(ABC):
         self.config.render_yaw, self.config.render_pitch,
         self.config.render_roll, 2)
     begin, count = (0, 1) if envs is None else (int(envs[0]), int(envs[1]))
-    w, h, rgb = self.client.getCameraImage(
+    w, h, rgb, _, _ = self.client.getCameraImage(
         self.config.render_width, self.config.render_height, view_matrix,
-        proj_matrix, env_begin=begin, env_count=count)
+        proj_matrix, env_begin=begin, env_count=count, depth=False, segmentation=False)
     if envs is None:
       # 4 channels for RGBA
       return np.reshape(rgb[0].cpu().numpy(), (h, w, 4))

@@ -264,12 +264,15 @@ int solo_solver_lanes(SoloHandle h);
  * solo_render rasterises environments [env_begin, env_begin + env_count) at their
  * current state into rgba_dev, uint8[env_count][height][width][4] (device), with two
  * launches on `stream`; scratch_dev holds solo_render_scratch_bytes(h, env_count)
- * bytes, 256-byte aligned.  No graphics API, no host round trip. */
+ * bytes, 256-byte aligned.  depth_dev (float[env_count][height][width], OpenGL depth in
+ * [0, 1], 1 = nothing hit) and seg_dev (int32, same shape: plane 0, robot 1, nothing -1)
+ * are getCameraImage's other two images; either may be NULL.  No graphics API, no host
+ * round trip. */
 int solo_bind_mesh(SoloHandle h, const int32_t *tri_body_dev, const float *tri_verts_dev,
                    const float *tri_rgba_dev, int32_t n_tri);
 int64_t solo_render_scratch_bytes(SoloHandle h, int32_t env_count);
 int solo_render(SoloHandle h, const SoloCamera *camera, int32_t env_begin, int32_t env_count,
-                uint8_t *rgba_dev, void *scratch_dev, void *stream);
+                uint8_t *rgba_dev, float *depth_dev, int32_t *seg_dev, void *scratch_dev, void *stream);
 /* Live per-kernel timing (bench.py roofline): while enabled every physics step
  * records CUDA events on the launching stream around its three kernels;
  * solo_phase_times synchronises on them and returns the number of physics

@@ -55,7 +55,9 @@ def _u8(c):
 
 
 def render(blob, visual, state, view, proj, width, height, light_direction, ambient, diffuse,
-           background, plane_rgb_a, plane_rgb_b, checker_size):
+           background, plane_rgb_a, plane_rgb_b, checker_size, aux=False):
+  """aux=True also returns getCameraImage's depth buffer (0.5 ndc_z + 0.5, 1 where nothing was
+  hit) and segmentation mask (plane 0, robot 1, nothing -1)."""
   W, H = int(width), int(height)
   V = np.asarray(view, dtype=np.float64).reshape(4, 4).T     # column-major input
   P = np.asarray(proj, dtype=np.float64).reshape(4, 4).T
@@ -66,6 +68,7 @@ def render(blob, visual, state, view, proj, width, height, light_direction, ambi
   img[..., :3] = _u8(np.asarray(background, dtype=np.float64))
   img[..., 3] = 255
   depth = np.full((H, W), 1.0)
+  seg = np.full((H, W), -1, dtype=np.int32)
 
   poses = body_poses(blob, state)
   xs = np.arange(W) + 0.5
@@ -100,6 +103,7 @@ def render(blob, visual, state, view, proj, width, height, light_direction, ambi
     hit = (w0 >= 0) & (w1 >= 0) & (w2 >= 0) & (z < sub) & (z >= -1.0)
     sub[hit] = z[hit]
     img[y0:y1, x0:x1, :3][hit] = colour
+    seg[y0:y1, x0:x1][hit] = 1
 
   # ground plane
   Rv, tv = V[:3, :3], V[:3, 3]
@@ -123,4 +127,8 @@ def render(blob, visual, state, view, proj, width, height, light_direction, ambi
   ca, cb = _u8(np.asarray(plane_rgb_a) * li), _u8(np.asarray(plane_rgb_b) * li)
   img[..., :3][hit & ~odd] = ca
   img[..., :3][hit & odd] = cb
-  return img
+  if not aux:
+    return img
+  depth = np.where(hit, z, depth)
+  seg[hit] = 0
+  return img, (0.5 * depth + 0.5).astype(np.float32), seg

@@ -5,6 +5,7 @@ of the checkerboard or a depth tie may pick the other side.  Stated tolerance:
 at most 0.3 % of the pixels differ by more than 1 grey level in any channel."""
 import numpy as np
 import pytest
+import torch
 
 from gym_solo_b200 import _abi, camera
 from oracle import solo_render_oracle as ro
@@ -90,14 +91,29 @@ def test_render_other_cameras_sizes_and_shading():
     w, h = k['size']
     view = c.computeViewMatrixFromYawPitchRoll([0, 0, .2], k['dist'], *k['ypr'], 2)
     proj = c.computeProjectionMatrixFOV(k['fov'], w / h, 0.01, 100)
-    ww, hh, rgba = c.getCameraImage(w, h, view, proj, env_begin=1, env_count=3, **k['shade'])
+    # pybullet's five return values: width, height, rgba, depth buffer, segmentation mask
+    ww, hh, rgba, depth, seg = c.getCameraImage(w, h, view, proj, env_begin=1, env_count=3, **k['shade'])
     assert (ww, hh) == (w, h) and tuple(rgba.shape) == (3, h, w, 4)
-    rgba = rgba.cpu().numpy()
+    assert tuple(depth.shape) == (3, h, w) and depth.dtype == torch.float32
+    assert tuple(seg.shape) == (3, h, w) and seg.dtype == torch.int32
+    rgba, depth, seg = rgba.cpu().numpy(), depth.cpu().numpy(), seg.cpu().numpy()
     opts = dict(_abi.RENDER_DEFAULTS, **k['shade'])
     for i in range(3):
-      want = ro.render(c.blob, vis, states[1 + i], view, proj, w, h, **opts)
+      want, want_depth, want_seg = ro.render(c.blob, vis, states[1 + i], view, proj, w, h, aux=True, **opts)
       bad = _mismatch(rgba[i], want)
       assert bad <= MAX_BAD_FRACTION, (k['size'], i, bad)
+      same = seg[i] == want_seg
+      assert 1.0 - same.mean() <= MAX_BAD_FRACTION, (k['size'], i, 1.0 - same.mean())
+      assert set(np.unique(seg[i])) <= {-1, 0, 1} and (seg[i] == 1).any()
+      # where both agree on what was hit, the depth buffers agree: 1e-6 on average (float32 ndc
+      # depth has 6e-8 resolution near the far plane, the oracle is float64), 2e-4 at worst (sliver
+      # triangles: their affine depth equation has coefficients of order 1 / area)
+      err = np.abs(depth[i] - want_depth)[same]
+      assert err.mean() <= 1e-6 and err.max() <= 2e-4, (err.mean(), err.max())
+      assert (depth[i][seg[i] == -1] == 1.0).all() and depth[i].min() >= 0.0
+    # the images that were not asked for are not produced
+    _, _, _, d0, s0 = c.getCameraImage(w, h, view, proj, env_begin=0, env_count=1, depth=False, segmentation=False)
+    assert d0 is None and s0 is None
 
 
 def test_render_argument_errors():

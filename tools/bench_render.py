@@ -36,12 +36,12 @@ def main():
   w, h = cfg.render_width, cfg.render_height
   out = torch.empty((count, h, w, 4), dtype=torch.uint8, device='cuda')
   for _ in range(3):
-    c.getCameraImage(w, h, view, proj, 0, count, out=out)
+    c.getCameraImage(w, h, view, proj, 0, count, out=out, depth=False, segmentation=False)
   torch.cuda.synchronize()
   e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
   e0.record()
   for _ in range(reps):
-    c.getCameraImage(w, h, view, proj, 0, count, out=out)
+    c.getCameraImage(w, h, view, proj, 0, count, out=out, depth=False, segmentation=False)
   e1.record()
   torch.cuda.synchronize()
   ms = e0.elapsed_time(e1) / reps
