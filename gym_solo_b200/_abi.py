@@ -147,7 +147,7 @@ def make_camera(view, proj, width, height, **shading):
 def load_visual(blob):
   """The render() mesh compiled next to the model blob (compile_model.py `visual`):
   dict(n_tri, tri_body, tri_verts [n_tri][9] body coordinates, tri_rgba)."""
-  path = os.path.join(MODELS_DIR, blob['name'] + '_visual.json')
+  path = os.path.join(blob.get('_dir', MODELS_DIR), blob['name'] + '_visual.json')
   if not os.path.exists(path):
     raise ValueError('no compiled render mesh for model %r' % blob['name'])
   with open(path) as f:
@@ -163,7 +163,9 @@ def load_model_blob(name_or_path):
   if not os.path.exists(path):
     path = os.path.join(MODELS_DIR, name_or_path + '.json')
   with open(path) as f:
-    return json.load(f)
+    blob = json.load(f)
+  blob['_dir'] = os.path.dirname(os.path.abspath(path))   # where its render mesh lives
+  return blob
 
 
 def make_model(blob, link_friction=None):

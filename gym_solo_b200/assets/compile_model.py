@@ -106,10 +106,15 @@ def parse_urdf(path):
     lim = j.find('limit')
     lo = float(lim.get('lower', '0')) if lim is not None else 0.
     hi = float(lim.get('upper', '0')) if lim is not None else 0.
+    dyn = j.find('dynamics')
     joints.append(dict(name=j.get('name'), type=j.get('type'),
                        parent=j.find('parent').get('link'),
                        child=j.find('child').get('link'),
-                       xyz=xyz, R=R, axis=axis, lower=lo, upper=hi))
+                       xyz=xyz, R=R, axis=axis, lower=lo, upper=hi,
+                       effort=float(lim.get('effort', '0')) if lim is not None else 0.,
+                       velocity=float(lim.get('velocity', '0')) if lim is not None else 0.,
+                       damping=float(dyn.get('damping', '0')) if dyn is not None else 0.,
+                       friction=float(dyn.get('friction', '0')) if dyn is not None else 0.))
   children = {n: [] for n in links}
   has_parent = set()
   for j in joints:
@@ -204,6 +209,25 @@ def principal_frame(I):
   if np.linalg.det(R) < 0:
     R[:, 2] *= -1
   return np.array([c[0] for c in cols]), R
+
+
+def mat_to_quat(R):
+  """Rotation matrix -> (x, y, z, w), w >= 0."""
+  t = R[0, 0] + R[1, 1] + R[2, 2]
+  if t > 0:
+    s = math.sqrt(t + 1.0) * 2
+    q = [(R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s, (R[1, 0] - R[0, 1]) / s, 0.25 * s]
+  else:
+    i = int(np.argmax([R[0, 0], R[1, 1], R[2, 2]]))
+    j, k = (i + 1) % 3, (i + 2) % 3
+    s = math.sqrt(R[i, i] - R[j, j] - R[k, k] + 1.0) * 2
+    q = [0.0, 0.0, 0.0, (R[k, j] - R[j, k]) / s]
+    q[i] = 0.25 * s
+    q[j] = (R[j, i] + R[i, j]) / s
+    q[k] = (R[k, i] + R[i, k]) / s
+  if q[3] < 0:
+    q = [-v for v in q]
+  return [float(v) + 0.0 for v in q]
 
 
 def compile_model(urdf_path, name=None, fallback_boxes=None, visual=None, visual_dirs=40):
@@ -350,6 +374,14 @@ def compile_model(urdf_path, name=None, fallback_boxes=None, visual=None, visual
       base_inertial_pos=base_com.tolist(), base_inertial_rot=Rb.tolist(),
       n_cand=len(cand_body), cand_body=cand_body, cand_pos=cand_pos,
       cand_mu=cand_mu, cand_link=cand_link, collision_margin=0.001,
+      # pre-merge data, for getJointInfo (assets/joint_info.py): every URDF link with the body it
+      # belongs to, its frame in that body's coordinates and its own inertial parameters
+      links=[dict(name=l, body=bi, pos=(p + 0.0).tolist(), rot=(R + 0.0).tolist(), mass=links[l]['mass'],
+                  com=links[l]['com'].tolist(), inertia=links[l]['I'].tolist())
+             for bi, body in enumerate(bodies) for l, p, R in body['parts']],
+      api_joints=[dict(name=j['name'], type=j['type'], parent=j['parent'], child=j['child'],
+                       effort=j['effort'], velocity=j['velocity'], damping=j['damping'],
+                       friction=j['friction']) for j in api],
   )
   if visual is not None:
     visual.update(name=model['name'], source=model['source'], n_tri=len(tri_body),

@@ -79,6 +79,7 @@ class BatchedClient:
     self._render_scratch = None
     self._link_friction = None
     self._base_mass_scale = None
+    self._joint_info = None
 
   # ---- render (solo8_base_env.py:116-142) ---------------------------------------
   def computeProjectionMatrixFOV(self, fov, aspect, nearVal, farVal):
@@ -390,14 +391,12 @@ class BatchedClient:
     return self.n_api
 
   def getJointInfo(self, body, j):
-    """Tuple shaped like pybullet's: [1] name (bytes), [2] type (0 revolute,
-    4 fixed), [8]/[9] limits, [12] child link name."""
-    name = self.blob['api_names'][j]
-    fixed = self.api_dof[j] < 0
-    return (j, name.encode('UTF-8'), 4 if fixed else 0, -1 if fixed else 7 + self.api_dof[j],
-            -1 if fixed else 6 + self.api_dof[j], 0, 0.0, 0.0,
-            float(self.model.api_lower[j]), float(self.model.api_upper[j]), 1000.0, 1000.0,
-            name.encode('UTF-8'))
+    """pybullet's 17-tuple, derived from the compiled model (assets/joint_info.py; the
+    golden tuples of gym_solo/core/test_obs_observations.py:123-162 are reproduced to 1e-9)."""
+    if self._joint_info is None:
+      from gym_solo_b200.assets.joint_info import joint_info
+      self._joint_info = joint_info(self.blob)
+    return self._joint_info[j]
 
   def getJointState(self, body, j):
     d = self.api_dof[j]
