@@ -68,7 +68,6 @@ EXPORTS = {
     'solo_phase_timing': (C.c_int, [C.c_void_p, C.c_int32]),
     'solo_phase_times': (C.c_int64, [C.c_void_p, C.POINTER(C.c_double)]),
     'solo_block_size': (C.c_int, [C.c_void_p]),
-    'solo_solver_lanes': (C.c_int, [C.c_void_p]),
     'solo_solver_stats': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     'solo_bind_mesh': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]),
     'solo_render_scratch_bytes': (C.c_int64, [C.c_void_p, C.c_int32]),

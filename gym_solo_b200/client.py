@@ -62,7 +62,7 @@ class BatchedClient:
     self.state = torch.zeros((self.sdim, self.n), dtype=torch.float32, device=dev)
     self.counters = torch.zeros((_abi.MAX_TERM_TERMS, self.n), dtype=torch.int32, device=dev)
     self.snapshot = torch.zeros((self.sdim,), dtype=torch.float32, device=dev)
-    self.stats = torch.zeros((4, self.n), dtype=torch.float32, device=dev)
+    self.stats = torch.zeros((5, self.n), dtype=torch.float32, device=dev)
     self.diag = torch.zeros((4,), dtype=torch.int64, device=dev)
     # solver scratch: per-env records for the solver warp, mass-matrix factors, yh, support points
     nbytes = int(self.lib.solo_scratch_bytes(self.handle))
@@ -80,6 +80,8 @@ class BatchedClient:
     self._link_friction = None
     self._base_mass_scale = None
     self._joint_info = None
+    self._randomisation_version = 0       # bumped by set_link_friction / set_base_mass_scale
+    self._per_env_snapshot_key = None
 
   # ---- render (solo8_base_env.py:116-142) ---------------------------------------
   def computeProjectionMatrixFOV(self, fov, aspect, nearVal, farVal):
@@ -198,6 +200,7 @@ class BatchedClient:
     t = torch.as_tensor(np.asarray(state, dtype=np.float32) if not torch.is_tensor(state) else state)
     t = t.to(device=self.device, dtype=torch.float32)
     per_env = t.dim() == 2
+    self._per_env_snapshot_key = None
     shape = (self.sdim, self.n) if per_env else (self.sdim,)
     if tuple(self.snapshot.shape) != shape:
       self.snapshot = torch.zeros(shape, dtype=torch.float32, device=self.device)
@@ -219,6 +222,12 @@ class BatchedClient:
       # settle runs for the whole batch, one snapshot per env
       pos_n = np.broadcast_to(np.asarray(pos, dtype=np.float64), (self.n, 3))
       eul_n = np.broadcast_to(np.asarray(euler, dtype=np.float64), (self.n, 3))
+      # settled once per (config, targets, poses, friction / payload version): later resets --
+      # masked ones included -- only run reset_kernel on the snapshot already bound
+      key = (_struct_key(cfg), tuple(float(x) for x in start_targets_api), pos_n.tobytes(), eul_n.tobytes(),
+             n_steps, self._randomisation_version)
+      if self._per_env_snapshot_key == key:
+        return None
       full = BatchedClient(self.blob, self.model, cfg, self.n, self.device)
       if self._link_friction is not None:
         _lib.check(self.lib.solo_bind_link_friction(full.handle, _ptr(self._link_friction)), full.handle)
@@ -230,6 +239,7 @@ class BatchedClient:
       snap = full.get_state()
       full.disconnect()
       self.set_snapshot(snap)
+      self._per_env_snapshot_key = key
       return snap.double().cpu().numpy()
     key = (_struct_key(self.model), _struct_key(cfg), tuple(float(x) for x in start_targets_api),
            tuple(pos), tuple(euler), n_steps, self.index)
@@ -311,6 +321,7 @@ class BatchedClient:
   def set_link_friction(self, friction):
     """Per-env lateral friction of the non-base links ([N], None restores the model's
     value for every env): changeDynamics(lateralFriction=...) per environment."""
+    self._randomisation_version += 1
     if friction is None:
       self._link_friction = None
       _lib.check(self.lib.solo_bind_link_friction(self.handle, None), self.handle)
@@ -323,6 +334,7 @@ class BatchedClient:
   def set_base_mass_scale(self, scale):
     """Per-env factor on the base body's mass and inertia ([N] > 0; None restores the
     model's base for every env)."""
+    self._randomisation_version += 1
     if scale is None:
       self._base_mass_scale = None
       _lib.check(self.lib.solo_bind_base_mass_scale(self.handle, None), self.handle)
@@ -370,9 +382,6 @@ class BatchedClient:
     _lib.check(self.lib.solo_solver_stats(self.handle, C.byref(ptr)), self.handle)
     off = (ptr.value - self.scratch.data_ptr())
     return self.scratch[off:off + 16 * self.n].view(torch.float32).view(4, self.n).clone()
-
-  def solver_lanes(self):
-    return int(self.lib.solo_solver_lanes(self.handle))
 
   # ---- BulletClient getters, batched -------------------------------------------
   def getBasePositionAndOrientation(self, body=ROBOT_ID):

@@ -18,6 +18,7 @@ import torch
 from gym_solo_b200 import _abi
 from gym_solo_b200 import solo_types
 from gym_solo_b200 import spaces
+from gym_solo_b200.core import _epoch
 
 
 class Observation(ABC):
@@ -98,6 +99,7 @@ class ObservationFactory:
         lbl_len, obs_len))
 
     self._observations.append(obs)
+    _epoch.bump()
 
   def get_obs(self) -> Tuple[solo_types.obs, List[str]]:
     """obs.py:130-159 (the non-fused path: one kernel / torch expression per
@@ -151,11 +153,9 @@ class ObservationFactory:
     terms = [o._fused_term(self._normalize) for o in self._observations]
     return None if any(t is None for t in terms) else terms
 
-  def signature(self):
-    return tuple(id(o) for o in self._observations) + (self._normalize,)
 
 
-class TorsoIMU(Observation):
+class TorsoIMU(_epoch.Tracked, Observation):
   """Orientation and velocities of the torso (obs.py:193-282)."""
   labels: List[str] = ['θx', 'θy', 'θz', 'vx', 'vy', 'vz', 'wx', 'wy', 'wz']
 
@@ -208,7 +208,7 @@ class TorsoIMU(Observation):
     return _run_single_term(self, self._fused_term(False), 9)
 
 
-class MotorEncoder(Observation):
+class MotorEncoder(_epoch.Tracked, Observation):
   """Position of all the joints, fixed ones included (obs.py:285-363)."""
 
   def __init__(self, body_id: int, degrees: bool = False,

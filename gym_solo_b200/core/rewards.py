@@ -22,6 +22,7 @@ import torch
 
 from gym_solo_b200 import _abi
 from gym_solo_b200 import solo_types
+from gym_solo_b200.core import _epoch
 
 
 class Reward(ABC):
@@ -109,6 +110,7 @@ class RewardFactory:
                   DeprecationWarning, stacklevel=2)
     reward.client = self._client
     self._rewards.append(_WeightedReward(reward=reward, weight=weight))
+    _epoch.bump()
 
   def get_reward(self):
     if not self._rewards:
@@ -125,11 +127,9 @@ class RewardFactory:
       return None
     return ops
 
-  def signature(self):
-    return tuple((id(wr.reward), wr.weight) for wr in self._rewards)
 
 
-class AdditiveReward(Reward):
+class AdditiveReward(_epoch.Tracked, Reward):
   """c1 r1 + c2 r2 + ... (rewards.py:121-160)."""
 
   def __init__(self):
@@ -140,6 +140,7 @@ class AdditiveReward(Reward):
     # caller set it (rewards.py:143)
     reward.client = self.client
     self._terms.append(_WeightedReward(reward=reward, weight=coefficient))
+    _epoch.bump()
 
   def compute(self):
     if not self._terms:
@@ -152,7 +153,7 @@ class AdditiveReward(Reward):
     return _weighted_program(self._terms, ops)
 
 
-class MultiplicitiveReward(Reward):
+class MultiplicitiveReward(_epoch.Tracked, Reward):
   """c * r1 * r2 * ... (rewards.py:163-199)."""
 
   def __init__(self, coefficient: float, *terms: Reward):
@@ -187,7 +188,7 @@ class MultiplicitiveReward(Reward):
       t.client = self._client
 
 
-class _Leaf(Reward):
+class _Leaf(_epoch.Tracked, Reward):
   """Built-in state reward: one op of the fused program."""
 
   def _leaf_op(self):

@@ -11,6 +11,7 @@ from abc import ABC, abstractmethod
 import torch
 
 from gym_solo_b200 import _abi
+from gym_solo_b200.core import _epoch
 
 
 class Termination(ABC):
@@ -39,6 +40,7 @@ class TerminationFactory:
 
   def register_termination(self, *terminations):
     self._terminations.extend(terminations)
+    _epoch.bump()
     if self._client is not None:
       self._attach_all()
 
@@ -85,11 +87,9 @@ class TerminationFactory:
     terms = [t._fused_term() for t in self._terminations]
     return None if any(t is None for t in terms) else terms
 
-  def signature(self):
-    return tuple((id(t), getattr(t, 'max_step_delta', None)) for t in self._terminations)
 
 
-class TimeBasedTermination(Termination):
+class TimeBasedTermination(_epoch.Tracked, Termination):
   """Terminates once step_delta exceeds max_step_delta, i.e. on call
   max_step_delta + 1 (termination.py:59-83)."""
 
@@ -146,7 +146,7 @@ class TimeBasedTermination(Termination):
     return t
 
 
-class PerpetualTermination(Termination):
+class PerpetualTermination(_epoch.Tracked, Termination):
   """Never ends (termination.py:86-98)."""
 
   def __init__(self):

@@ -72,11 +72,12 @@ struct DeviceGuard {
 };
 
 static int pick_block(int n_envs) {
-  const char *e = getenv("SOLO_BLOCK");
-  if (e) {
+#ifdef SOLO_EXPERIMENTS
+  if (const char *e = getenv("SOLO_BLOCK")) {   // A/B builds only (tools/): never in the product library
     int b = atoi(e);
     if (b == 32 || b == 64 || b == 128) return b;
   }
+#endif
   // 148 SMs: keep every SM busy for small batches, fewer larger blocks once
   // there are several warps per SM anyway
   if (n_envs <= 148 * 64) return 32;
@@ -193,10 +194,12 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->block = pick_block(n_envs);
   {
     // setup phase: one lane per (environment, leg) -- faster at every batch size measured
-    // (4096: 0.031 -> 0.019 ms, 65536: 0.159 -> 0.138 ms); SOLO_SETUP=serial keeps the
-    // one-thread-per-environment kernel (A/B runs)
-    const char *e = getenv("SOLO_SETUP");
-    h->legpar = !(e && strcmp(e, "serial") == 0);
+    // (4096: 0.031 -> 0.019 ms, 65536: 0.159 -> 0.138 ms).  The one-thread-per-environment
+    // kernel exists only in -DSOLO_EXPERIMENTS builds (SOLO_SETUP=serial, A/B runs).
+    h->legpar = true;
+#ifdef SOLO_EXPERIMENTS
+    if (const char *e = getenv("SOLO_SETUP")) h->legpar = strcmp(e, "serial") != 0;
+#endif
     if (h->legpar && h->block > 64) h->block = 64;   // 4 lanes per environment, 256-thread blocks
   }
   h->motor_mask = 0;
@@ -249,12 +252,16 @@ int solo_set_program(SoloHandle h, const SoloProgram *program) {
   const size_t sm = tile_smem(h);
   int rc = SOLO_OK;
   if (h->ch == 2) {
+#ifdef SOLO_EXPERIMENTS
     if (!rc) rc = opt_in_smem(h, setup_kernel<2>, sm);
+#endif
     if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<2>, sm);
     if (!rc) rc = opt_in_smem(h, finish_kernel<2>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<2>, sm);
   } else {
+#ifdef SOLO_EXPERIMENTS
     if (!rc) rc = opt_in_smem(h, setup_kernel<3>, sm);
+#endif
     if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<3>, sm);
     if (!rc) rc = opt_in_smem(h, finish_kernel<3>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<3>, sm);
@@ -389,8 +396,11 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
   }
 #define SOLO_MARK(i) do { if (ev) cudaEventRecord(ev[i], st); } while (0)
   if (h->ch == 2) {
-    if (h->legpar) setup_legpar_kernel<2><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    else setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+#ifdef SOLO_EXPERIMENTS
+    if (!h->legpar) setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+    else
+#endif
+    setup_legpar_kernel<2><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
     if (dbg) solve_warp_kernel<2, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
@@ -399,8 +409,11 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     SOLO_MARK(2);
     finish_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
   } else {
-    if (h->legpar) setup_legpar_kernel<3><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    else setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+#ifdef SOLO_EXPERIMENTS
+    if (!h->legpar) setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
+    else
+#endif
+    setup_legpar_kernel<3><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
     if ((rc = check_launch(h, "setup_kernel"))) return rc;
     SOLO_MARK(1);
     if (dbg) solve_warp_kernel<3, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
@@ -538,8 +551,6 @@ int solo_solver_stats(SoloHandle h, const float **stats_dev) {
   *stats_dev = h->B.yh + (size_t)(6 + kLegs * h->ch) * (size_t)h->B.n;
   return SOLO_OK;
 }
-
-int solo_solver_lanes(SoloHandle h) { return h ? 0 : SOLO_EINVAL; }   // one warp per environment
 
 // ---- render() ------------------------------------------------------------------------
 int solo_bind_mesh(SoloHandle h, const int32_t *tri_body_dev, const float *tri_verts_dev,

@@ -190,6 +190,18 @@ template <typename T> SOLO_HD S3<T> rotate_inertia(const M3<T> &R, const T *I6) 
   o.yy = dot(r1, t1); o.yz = dot(r1, t2); o.zz = dot(r2, t2);
   return o;
 }
+// Composite (mass m, first moment h, inertia I) about a reference point -> about the point
+// that sees every mass at r + d (new reference = old reference - d).
+template <typename T> SOLO_HD void shift_composite(const T m, V3<T> &h, S3<T> &I, const V3<T> d) {
+  const T s = 2 * dot(h, d) + m * dot(d, d);
+  I.xx += s - 2 * h.x * d.x - m * d.x * d.x;
+  I.yy += s - 2 * h.y * d.y - m * d.y * d.y;
+  I.zz += s - 2 * h.z * d.z - m * d.z * d.z;
+  I.xy -= h.x * d.y + d.x * h.y + m * d.x * d.y;
+  I.xz -= h.x * d.z + d.x * h.z + m * d.x * d.z;
+  I.yz -= h.y * d.z + d.y * h.z + m * d.y * d.z;
+  h = h + d * m;
+}
 template <typename T> SOLO_HD M3<T> quat_to_mat(const T *q) {
   T x = q[0], y = q[1], z = q[2], w = q[3];
   T s = T(2) / (x * x + y * y + z * z + w * w);

@@ -9,9 +9,9 @@
 //                  parallel, their sums by xor-shuffle, the 6 x 6 base part on all
 //                  four lanes); writes the factors [k][env] for finish_kernel and one
 //                  contiguous KinLayout record per environment for the solver warp.
-//                  setup_kernel below is the one-thread-per-environment form of the
-//                  same phase (setup_step of solo_setup.h, shared with the host
-//                  tests), kept for A/B runs (SOLO_SETUP=serial).
+//                  (setup_step of solo_setup.h is the one-thread-per-environment
+//                  statement of the same phase, which tests/hostsim runs on the CPU;
+//                  as a kernel it exists only in -DSOLO_EXPERIMENTS builds.)
 //   solve_warp_kernel (solo_solve_warp.cuh)  one warp per environment: contact
 //                  detection and contact rows one contact per lane, then the
 //                  data-dependent part: projected Gauss-Seidel, a serial chain
@@ -47,7 +47,8 @@ struct Buffers {
   float *state;              // [state_dim][n]
   int32_t *counters;         // [kMaxTermTerms][n]
   const float *snapshot;     // [state_dim], or [state_dim][n] when snapshot_per_env (solo_snapshot_layout)
-  float *stats;              // [4][n] or null: running return, running length, last return, episodes
+  float *stats;              // [5][n] or null: running return, running length, sum of finished returns,
+                             // finished episodes, sum of finished lengths
   unsigned long long *diag;  // [4] or null: contacts, PGS iterations, NaN restores, physics steps
   float *dbg_normal_force;   // [n_cand][n] or null
   float *dbg_motor_torque;   // [ndof][n] or null
@@ -149,6 +150,7 @@ __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0
   }
 }
 
+#ifdef SOLO_EXPERIMENTS   // one thread per environment: A/B builds only, not in the product library
 // ---------------------------------------------------------------------------------
 // phase 1: setJointMotorControlArray + the pre-solver half of stepSimulation
 // (solo8v2vanilla.py:87-91)
@@ -183,6 +185,7 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
   setup_step<float, CH, false>(M, K.C, s, cmd, nullptr, kin + KL::kMotor, RL::kRow, B.fac + env, B.n, kin,
                                B.base_mass_scale ? B.base_mass_scale[env] : 1.f);
 }
+#endif  // SOLO_EXPERIMENTS
 
 // ---------------------------------------------------------------------------------
 // phase 3: velocity update + integration, then (epilogue != 0) the rest of
@@ -217,7 +220,15 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
 #pragma unroll
       for (int k = 0; k < CH; k++) yl[l][k] = y[(int64_t)(6 + l * CH + k) * B.n];
     finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
-    if (!env_finite<CH>(s)) { load_snapshot<CH>(M, B, env, s); nan = 1; }
+    // A non-finite state ends the episode: the environment restarts from its reset snapshot, the
+    // step reports done = 1 (epilogue steps), the termination counters and the running episode
+    // statistics start over, and diag[2] counts it (pybullet would hand the NaN to the caller).
+    if (!env_finite<CH>(s)) {
+      load_snapshot<CH>(M, B, env, s);
+      nan = 1;
+      for (int t = 0; t < kMaxTermTerms; t++) B.counters[(int64_t)t * B.n + env] = 0;
+      if (B.stats && !epilogue) { B.stats[env] = 0.f; B.stats[(int64_t)B.n + env] = 0.f; }
+    }
   }
   if (B.diag) {
     // fold this step's per-env solver statistics into the running totals
@@ -235,13 +246,19 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
     compute_obs<float, CH>(M, P, s, e, ob);
     rew = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
     done = eval_terminations(P, B.counters + env, B.n);
+    if (nan) {
+      done = true;   // restarted from the snapshot above: the new episode has not ticked yet
+      for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
+    }
     if (B.stats) {
       float ret = B.stats[env] + rew;
       float len = B.stats[(int64_t)B.n + env] + 1.f;
       if (done) {
-        B.stats[2 * (int64_t)B.n + env] = ret;
+        // totals over FINISHED episodes (episode_statistics: mean return / mean length)
+        B.stats[2 * (int64_t)B.n + env] += ret;
         B.stats[3 * (int64_t)B.n + env] += 1.f;
-        if (P.auto_reset) { ret = 0.f; len = 0.f; }
+        B.stats[4 * (int64_t)B.n + env] += len;
+        if (P.auto_reset || nan) { ret = 0.f; len = 0.f; }
       }
       B.stats[env] = ret;
       B.stats[(int64_t)B.n + env] = len;

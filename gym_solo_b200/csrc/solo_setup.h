@@ -126,22 +126,27 @@ SOLO_LEG_LOOP
         }
       }
     }
-    // tip -> root: bias generalised forces and composite inertia
-    V3<T> Fs = mk(T(0), T(0), T(0)), Ns = Fs, ch = Fs;
+    // tip -> root: bias generalised forces and composite inertia.  Everything a joint sees is
+    // accumulated ABOUT THAT JOINT'S OWN ORIGIN (shifted link by link), not about the base COM:
+    // the leg block D of a few-gram distal link is then a sum of small terms instead of the
+    // difference of two large ones (MMR v4: joint-rate error 5e-3 -> the common tolerance).
+    V3<T> Fs = mk(T(0), T(0), T(0)), Ns = Fs, ch = Fs;   // Ns, ch, cI: about jo[l][j]
     T cm = 0;
     S3<T> cI; cI.xx = cI.xy = cI.xz = cI.yy = cI.yz = cI.zz = 0;
-    V3<T> v0j[CH];   // linear velocity at c0 of a unit rate of joint j
     V3<T> Bp[CH], BL[CH];
     T D[CH][CH];
     T fl[CH];
 #pragma unroll
-    for (int j = 0; j < CH; j++) v0j[j] = cross(ja[l][j], c0 - jo[l][j]);
-#pragma unroll
     for (int j = CH - 1; j >= 0; j--) {
-      const V3<T> r = bc[j] - c0;
+      if (j < CH - 1) {
+        const V3<T> d = jo[l][j + 1] - jo[l][j];
+        Ns = Ns + cross(d, Fs);
+        shift_composite(cm, ch, cI, d);
+      }
+      const V3<T> r = bc[j] - jo[l][j];
       Fs = Fs + F[j];
       Ns = Ns + cross(r, F[j]) + N[j];
-      const T Cj = dot(ja[l][j], Ns - cross(jo[l][j] - c0, Fs));
+      const T Cj = dot(ja[l][j], Ns);
       T tau = 0;
       if (C.control_mode == 1) tau = m_clamp(cmd[l][j], -C.torque_limit, C.torque_limit);
       fl[j] = act[j] ? tau - Cj : T(0);
@@ -152,15 +157,22 @@ SOLO_LEG_LOOP
       cI.xx += bI[j].xx + mb * (rr - r.x * r.x); cI.xy += bI[j].xy - mb * r.x * r.y;
       cI.xz += bI[j].xz - mb * r.x * r.z;        cI.yy += bI[j].yy + mb * (rr - r.y * r.y);
       cI.yz += bI[j].yz - mb * r.y * r.z;        cI.zz += bI[j].zz + mb * (rr - r.z * r.z);
-      const V3<T> p = v0j[j] * cm + cross(ja[l][j], ch);
-      const V3<T> L = mul(cI, ja[l][j]) + cross(ch, v0j[j]);
-      Bp[j] = p; BL[j] = L;
+      // momentum of the subtree under a unit rate of joint j: linear p, angular n about jo[l][j]
+      const V3<T> p = cross(ja[l][j], ch);
+      const V3<T> n = mul(cI, ja[l][j]);
+      Bp[j] = p; BL[j] = n + cross(jo[l][j] - c0, p);   // base coupling: angular part about c0
 #pragma unroll
       for (int jj = 0; jj <= j; jj++) {
-        T v = dot(v0j[jj], p) + dot(ja[l][jj], L);
+        T v = dot(ja[l][jj], n + cross(jo[l][j] - jo[l][jj], p));
         D[j][jj] = v; D[jj][j] = v;
       }
       if (!act[j]) D[j][j] = 1;   // dummy unit dof, zero coupling
+    }
+    {
+      // leg totals about the base COM
+      const V3<T> d = jo[l][0] - c0;
+      Ns = Ns + cross(d, Fs);
+      shift_composite(cm, ch, cI, d);
     }
     Ftot = Ftot + Fs; Ntot = Ntot + Ns;
     mtot += cm; htot = htot + ch;

@@ -138,19 +138,24 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
     }
   }
   // ---- own leg: tip -> root, generalised bias forces, composite inertia, leg block ----
+  // accumulated about each joint's own origin, shifted link by link (see setup_step): no
+  // cancellation in the leg block of a few-gram distal link
   V3<T> Fs = mk(0.f, 0.f, 0.f), Ns = Fs, ch = Fs;
   T cm = 0.f;
   S3<T> cI; cI.xx = cI.xy = cI.xz = cI.yy = cI.yz = cI.zz = 0.f;
-  V3<T> v0j[CH], Bp[CH], BL[CH];
+  V3<T> Bp[CH], BL[CH];
   T D[CH][CH], fl[CH];
 #pragma unroll
-  for (int j = 0; j < CH; j++) v0j[j] = cross(ja[j], c0 - jo[j]);
-#pragma unroll
   for (int j = CH - 1; j >= 0; j--) {
-    const V3<T> r = bc[j] - c0;
+    if (j < CH - 1) {
+      const V3<T> d = jo[j + 1] - jo[j];
+      Ns = Ns + cross(d, Fs);
+      shift_composite(cm, ch, cI, d);
+    }
+    const V3<T> r = bc[j] - jo[j];
     Fs = Fs + F[j];
     Ns = Ns + cross(r, F[j]) + N[j];
-    const T Cj = dot(ja[j], Ns - cross(jo[j] - c0, Fs));
+    const T Cj = dot(ja[j], Ns);
     T tau = 0.f;
     if (C.control_mode == 1) tau = m_clamp(cmd[j], -C.torque_limit, C.torque_limit);
     fl[j] = act[j] ? tau - Cj : 0.f;
@@ -161,15 +166,21 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
     cI.xx += bI[j].xx + mb * (rr - r.x * r.x); cI.xy += bI[j].xy - mb * r.x * r.y;
     cI.xz += bI[j].xz - mb * r.x * r.z;        cI.yy += bI[j].yy + mb * (rr - r.y * r.y);
     cI.yz += bI[j].yz - mb * r.y * r.z;        cI.zz += bI[j].zz + mb * (rr - r.z * r.z);
-    const V3<T> p = v0j[j] * cm + cross(ja[j], ch);
-    const V3<T> L = mul(cI, ja[j]) + cross(ch, v0j[j]);
-    Bp[j] = p; BL[j] = L;
+    const V3<T> p = cross(ja[j], ch);
+    const V3<T> n = mul(cI, ja[j]);
+    Bp[j] = p; BL[j] = n + cross(jo[j] - c0, p);
 #pragma unroll
     for (int jj = 0; jj <= j; jj++) {
-      const T v = dot(v0j[jj], p) + dot(ja[jj], L);
+      const T v = dot(ja[jj], n + cross(jo[j] - jo[jj], p));
       D[j][jj] = v; D[jj][j] = v;
     }
     if (!act[j]) D[j][j] = 1.f;   // dummy unit dof, zero coupling
+  }
+  {
+    // leg totals about the base COM
+    const V3<T> d = jo[0] - c0;
+    Ns = Ns + cross(d, Fs);
+    shift_composite(cm, ch, cI, d);
   }
   chol_inverse_lower<T, CH>(D);   // D <- C^-1 (lower) = E
   T Bh[CH][6], fh[CH];

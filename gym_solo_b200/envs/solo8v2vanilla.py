@@ -19,6 +19,7 @@ from gym_solo_b200 import _abi
 from gym_solo_b200 import client as bclient
 from gym_solo_b200 import solo_types
 from gym_solo_b200 import spaces
+from gym_solo_b200.core import _epoch
 from gym_solo_b200.core.configs import Solo8BaseConfig
 from gym_solo_b200.envs.solo8_base_env import Solo8BaseEnv
 
@@ -122,8 +123,9 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     """Compile the registered observations / rewards / terminations into the
     kernel's descriptor tables; None when any of them is a user subclass (or a
     factory is empty: the Python path then raises the reference's ValueError)."""
-    sig = (self.obs_factory.signature(), self.reward_factory.signature(),
-           self.termination_factory.signature(), self._auto_reset)
+    # one integer moves whenever a registration, an add_term or an attribute of a built-in
+    # plug-in changes (core/_epoch.py): the descriptor tables are recompiled then
+    sig = (_epoch.value, self._auto_reset)
     if sig == self._plan_sig:
       return self._plan
     self._plan_sig, self._plan = sig, None
@@ -261,12 +263,13 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     self.client.set_state(state)
 
   def episode_statistics(self, all_gather: bool = False):
-    """Mean return / length of finished episodes and counts for this rank's
-    shard; with all_gather=True (torch.distributed initialised) the four numbers
-    of every rank, [world, 4] -- the only collective of the framework."""
+    """Totals over the FINISHED episodes of this rank's shard -- sum of returns, sum of
+    lengths, number of episodes -- and the NaN restarts (sharding.summarize turns them into
+    episode-weighted means); with all_gather=True (torch.distributed initialised) the four
+    numbers of every rank, [world, 4] -- the only collective of the framework.  The kernel
+    accumulates the totals when an episode ends (fused built-in programs)."""
     st = self.client.stats
-    episodes = st[3].sum()
-    mine = torch.stack([st[2].sum(), st[1].sum(), episodes,
+    mine = torch.stack([st[2].sum(), st[4].sum(), st[3].sum(),
                         self.client.diag[2].to(torch.float32)])
     if not all_gather:
       return mine

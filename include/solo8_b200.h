@@ -179,8 +179,9 @@ int64_t solo_scratch_bytes(SoloHandle h);
 /* Bind caller-owned device buffers.  state_dev: float[SOLO_STATE_DIM][n_envs];
  * counters_dev: int32[SOLO_MAX_TERM_TERMS][n_envs]; snapshot_dev:
  * float[SOLO_STATE_DIM] post-reset state (solo8v2vanilla.py:124-136 computed
- * once); stats_dev: float[4][n_envs] episode return / length / last return /
- * episodes (may be NULL); scratch_dev: solo_scratch_bytes() bytes (may be NULL
+ * once); stats_dev: float[5][n_envs] (may be NULL): running return and length
+ * of the episode in progress, then totals over FINISHED episodes -- sum of
+ * returns, number of episodes, sum of lengths; scratch_dev: solo_scratch_bytes() bytes (may be NULL
  * when that is 0). */
 int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev,
               float *snapshot_dev, float *stats_dev, void *scratch_dev);
@@ -254,9 +255,6 @@ int solo_block_size(SoloHandle h);
  * inside the bound scratch: PGS iterations, contact points, contact points that
  * carried an impulse, SM cycles spent in the solve. */
 int solo_solver_stats(SoloHandle h, const float **stats_dev);
-/* Environments per warp of the solver kernel: always 0 = one WARP per
- * environment (kept for callers of the earlier lane-per-environment solver). */
-int solo_solver_lanes(SoloHandle h);
 /* render() -- gym_solo/envs/solo8_base_env.py:116-142 (getCameraImage).  The
  * mesh is a triangle soup in BODY coordinates (body 0 = base inertial frame, body
  * d + 1 = link of dof d), device pointers owned by the caller: tri_body

@@ -110,10 +110,16 @@ def test_termination_sequence_matches_reference():
   assert [int(a.step_delta[0]), int(c.step_delta[0])] == list(G['term_counters_end'])
 
 
-def test_action_normalisation_matches_reference():
-  """solo8v2vanilla.py:84-85: a * float32(2 pi), carried in float64."""
-  high = np.float32(2 * np.pi)
-  np.testing.assert_allclose(G['norm_actions_in'] * high, G['norm_actions_out'], rtol=0, atol=0)
+def test_action_normalisation_scale_is_the_float32_bound():
+  """solo8v2vanilla.py:84-85: a * self._action_space.high, a float32 Box bound.
+  The scale Solo8VanillaEnv._scale() hands to the kernel is spaces.Box(...).high[0]; the
+  reference's outputs (golden) are its inputs times exactly that number.  The kernel side
+  (action_scale in setup_legpar_kernel) is tested on the GPU: test_gpu_configs.py."""
+  from gym_solo_b200 import spaces
+  from gym_solo_b200.core.configs import Solo8BaseConfig
+  high = spaces.Box(-Solo8BaseConfig.max_motor_rotation, Solo8BaseConfig.max_motor_rotation, shape=(12,)).high
+  assert high.dtype == np.float32 and float(high[0]) == 6.2831854820251465
+  np.testing.assert_array_equal(G['norm_actions_in'] * float(high[0]), G['norm_actions_out'])
 
 
 # ---- known answers quoted from the reference's tests -------------------------------
