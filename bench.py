@@ -3,8 +3,9 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--envs E] [--impl reference]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A "step" is one env.step() of every environment of the batch (one fused kernel
-launch per rank).  Workload = BASELINE.json configs[1]: Solo8VanillaEnv, 4096
+A "step" is one env.step() of every environment of the batch: three kernels
+(setup -> solve -> finish) per physics substep, replayed as one captured CUDA
+graph per rank.  Workload = BASELINE.json configs[1]: Solo8VanillaEnv, 4096
 envs per GPU, POSITION_CONTROL, flat ground, dt = 1/240, TorsoIMU +
 MotorEncoder observations (21), 1 x UprightReward, PerpetualTermination, fresh
 U(-2pi, 2pi) actions every step (generated on the device outside the timed

@@ -34,6 +34,9 @@ REW_CONST = 6
 REW_ADD = 16
 REW_MUL = 17
 
+OPT_GRAPH = 1
+OPT_ZERO_COPY = 2
+
 TERM_PERPETUAL = 1
 TERM_TIME = 2
 

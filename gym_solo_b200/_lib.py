@@ -64,6 +64,7 @@ EXPORTS = {
     'solo_reset': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     'solo_step_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p]),
+    'solo_set_option': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     'solo_launch_count': (C.c_int64, [C.c_void_p]),
     'solo_phase_timing': (C.c_int, [C.c_void_p, C.c_int32]),
     'solo_phase_times': (C.c_int64, [C.c_void_p, C.POINTER(C.c_double)]),

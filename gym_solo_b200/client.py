@@ -358,6 +358,10 @@ class BatchedClient:
       _lib.check(self.lib.solo_bind_debug(self.handle, None, None), self.handle)
     return self._dbg
 
+  def set_option(self, option, value):
+    """solo_set_option: _abi.OPT_GRAPH / _abi.OPT_ZERO_COPY (both on by default)."""
+    _lib.check(self.lib.solo_set_option(self.handle, int(option), int(value)), self.handle)
+
   def launch_count(self):
     return int(self.lib.solo_launch_count(self.handle))
 

@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/solo8_b200.h"
@@ -34,6 +35,18 @@ struct SoloHandle_ {
   float *st_actions, *st_obs, *st_reward;
   uint8_t *st_done;
   int64_t launches;
+  // one env.step as ONE graph launch: the (setup, solve, finish) x substeps chain of solo_step is
+  // captured once per set of output buffers and replayed; only the action pointer of the setup
+  // nodes is patched per call.  Anything baked into the kernel parameters (bindings, program)
+  // bumps `epoch` and retires the captured graphs.
+  bool use_graph;
+  uint64_t epoch;
+  std::vector<struct StepGraph *> graphs;
+  cudaStream_t gstream;   // capture / replay stream when the caller's is the legacy default stream
+  // zero-copy host entry: device aliases of the caller's pinned result buffers (solo_step_host)
+  bool zero_copy;
+  const void *map_key[3];
+  void *map_dev[3];
   // render(): triangle mesh in body coordinates (device, caller-owned)
   const int32_t *tri_body;
   const float *tri_verts, *tri_rgba;
@@ -163,6 +176,66 @@ static std::string make_render_params(const SoloCamera &cam, RenderParams *out) 
   return "";
 }
 
+// ---- launches ------------------------------------------------------------------------
+// pdl: programmatic dependent launch -- the kernel may be scheduled while its predecessor in
+// the stream is still running; it calls cudaGridDependencySynchronize() before it touches
+// anything the predecessor writes (solve_warp_kernel, finish_kernel).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_ex(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, bool pdl,
+                             Args &&...args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
+// Argument block of one captured setup node (cudaGraphExecKernelNodeSetParams wants every
+// argument again when one changes).
+struct SetupArgs {
+  KParams K;
+  Buffers B;
+  const float *actions;
+  int broadcast;
+  float scale;
+  void *ptrs[5];
+  SetupArgs() { ptrs[0] = &K; ptrs[1] = &B; ptrs[2] = &actions; ptrs[3] = &broadcast; ptrs[4] = &scale; }
+  SetupArgs(const SetupArgs &o) : K(o.K), B(o.B), actions(o.actions), broadcast(o.broadcast), scale(o.scale) {
+    ptrs[0] = &K; ptrs[1] = &B; ptrs[2] = &actions; ptrs[3] = &broadcast; ptrs[4] = &scale;
+  }
+};
+
+struct StepGraph {
+  cudaGraph_t graph;
+  cudaGraphExec_t exec;
+  std::vector<cudaGraphNode_t> setup_nodes;
+  std::vector<cudaKernelNodeParams> setup_params;
+  SetupArgs *args;            // one block shared by the setup nodes of the substeps
+  const float *actions;       // what the nodes currently point at
+  float scale;
+  float *obs, *reward, *terminal;
+  uint8_t *done;
+  uint64_t epoch, used;
+};
+
+static void drop_graphs(SoloHandle h) {
+  for (StepGraph *g : h->graphs) {
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->graph) cudaGraphDestroy(g->graph);
+    delete g->args;
+    delete g;
+  }
+  h->graphs.clear();
+}
+static void touch(SoloHandle h) { h->epoch++; }   // kernel parameters changed: captured graphs are stale
+
 extern "C" {
 
 const char *solo_version(void) { return "solo8_b200 0.1 (sm_100a)"; }
@@ -212,6 +285,12 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   h->st_actions = h->st_obs = h->st_reward = nullptr;
   h->st_done = nullptr;
   h->launches = 0;
+  h->use_graph = true;
+  h->epoch = 1;
+  h->gstream = nullptr;
+  h->zero_copy = true;
+  h->map_key[0] = h->map_key[1] = h->map_key[2] = nullptr;
+  h->map_dev[0] = h->map_dev[1] = h->map_dev[2] = nullptr;
   h->tri_body = nullptr;
   h->tri_verts = h->tri_rgba = nullptr;
   h->n_tri = 0;
@@ -234,7 +313,12 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
 
 int solo_destroy(SoloHandle h) {
   if (!h) return SOLO_EINVAL;
-  for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
+  {
+    DeviceGuard g(h->device);
+    drop_graphs(h);
+    if (h->gstream) cudaStreamDestroy(h->gstream);
+    for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
+  }
   delete h;
   return SOLO_OK;
 }
@@ -245,6 +329,7 @@ int solo_set_program(SoloHandle h, const SoloProgram *program) {
   std::string msg = check_program(*program, h->K.M.n_api, &dim);
   if (!msg.empty()) return fail(h, SOLO_EINVAL, msg);
   memcpy(&h->K.P, program, sizeof h->K.P);
+  touch(h);
   h->obs_dim = dim;
   h->B.obs_dim = dim;
   h->program_set = true;
@@ -306,6 +391,7 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
     cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof(float) * tab_v.size(), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return cuda_fail(h, e, "upload of the support-point table");
   }
+  touch(h);
   h->B.state = state_dev;
   h->B.counters = counters_dev;
   h->B.snapshot = snapshot_dev;
@@ -316,30 +402,35 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
 
 int solo_snapshot_layout(SoloHandle h, int32_t per_env) {
   if (!h) return SOLO_EINVAL;
+  touch(h);
   h->B.snapshot_per_env = per_env ? 1 : 0;
   return SOLO_OK;
 }
 
 int solo_bind_diag(SoloHandle h, unsigned long long *diag_dev) {
   if (!h) return SOLO_EINVAL;
+  touch(h);
   h->B.diag = diag_dev;
   return SOLO_OK;
 }
 
 int solo_bind_link_friction(SoloHandle h, const float *link_friction_dev) {
   if (!h) return SOLO_EINVAL;
+  touch(h);
   h->B.link_friction = link_friction_dev;
   return SOLO_OK;
 }
 
 int solo_bind_base_mass_scale(SoloHandle h, const float *scale_dev) {
   if (!h) return SOLO_EINVAL;
+  touch(h);
   h->B.base_mass_scale = scale_dev;
   return SOLO_OK;
 }
 
 int solo_bind_debug(SoloHandle h, float *normal_force_dev, float *motor_torque_dev) {
   if (!h) return SOLO_EINVAL;
+  touch(h);
   h->B.dbg_normal_force = normal_force_dev;
   h->B.dbg_motor_torque = motor_torque_dev;
   return SOLO_OK;
@@ -375,7 +466,11 @@ static int drain_phase_events(SoloHandle h) {
 }
 
 // One physics step = setup -> solve -> finish on `st`.  epilogue != 0 makes the
-// finish kernel also run observations / reward / termination.
+// finish kernel also run observations / reward / termination.  The solver and the finish
+// kernel are programmatic dependents of the kernel in front of them: their blocks are
+// scheduled while it drains and wait (cudaGridDependencySynchronize) before they read what
+// it wrote.  With per-phase timing on, events sit between the kernels and the launches are
+// plain ones.
 static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast, float action_scale, int epilogue,
                           float *obs_dev, float *reward_dev, uint8_t *done_dev, float *terminal_obs_dev,
                           cudaStream_t st) {
@@ -394,35 +489,39 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     h->ev_used += 4;
     cudaEventRecord(ev[0], st);
   }
+  const bool pdl = !h->timing;
 #define SOLO_MARK(i) do { if (ev) cudaEventRecord(ev[i], st); } while (0)
-  if (h->ch == 2) {
+#define SOLO_PHYSICS(CH)                                                                                          \
+  do {                                                                                                            \
+    SOLO_SETUP_LAUNCH(CH);                                                                                        \
+    if ((rc = check_launch(h, "setup_kernel"))) return rc;                                                        \
+    SOLO_MARK(1);                                                                                                 \
+    if (dbg) launch_ex(solve_warp_kernel<CH, true>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,     \
+                       n_cand, margin);                                                                           \
+    else launch_ex(solve_warp_kernel<CH, false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,       \
+                   n_cand, margin);                                                                               \
+    if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
+    SOLO_MARK(2);                                                                                                 \
+    launch_ex(finish_kernel<CH>, grid, h->block, sm, st, pdl, h->K, h->B, epilogue, obs_dev, reward_dev,          \
+              done_dev, terminal_obs_dev);                                                                        \
+  } while (0)
 #ifdef SOLO_EXPERIMENTS
-    if (!h->legpar) setup_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    else
+#define SOLO_SETUP_LAUNCH(CH)                                                                                     \
+  do {                                                                                                            \
+    if (!h->legpar) setup_kernel<CH><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale); \
+    else launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, sm, st, false, h->K, h->B, actions_dev,           \
+                   broadcast, action_scale);                                                                      \
+  } while (0)
+#else
+#define SOLO_SETUP_LAUNCH(CH)                                                                                     \
+  launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, sm, st, false, h->K, h->B, actions_dev, broadcast,       \
+            action_scale)
 #endif
-    setup_legpar_kernel<2><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    if ((rc = check_launch(h, "setup_kernel"))) return rc;
-    SOLO_MARK(1);
-    if (dbg) solve_warp_kernel<2, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
-    else solve_warp_kernel<2, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
-    if ((rc = check_launch(h, "solve_kernel"))) return rc;
-    SOLO_MARK(2);
-    finish_kernel<2><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
-  } else {
-#ifdef SOLO_EXPERIMENTS
-    if (!h->legpar) setup_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    else
-#endif
-    setup_legpar_kernel<3><<<grid, 4 * h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale);
-    if ((rc = check_launch(h, "setup_kernel"))) return rc;
-    SOLO_MARK(1);
-    if (dbg) solve_warp_kernel<3, true><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
-    else solve_warp_kernel<3, false><<<h->B.n, 32, 0, st>>>(h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);
-    if ((rc = check_launch(h, "solve_kernel"))) return rc;
-    SOLO_MARK(2);
-    finish_kernel<3><<<grid, h->block, sm, st>>>(h->K, h->B, epilogue, obs_dev, reward_dev, done_dev, terminal_obs_dev);
-  }
+  if (h->ch == 2) SOLO_PHYSICS(2);
+  else SOLO_PHYSICS(3);
   SOLO_MARK(3);
+#undef SOLO_SETUP_LAUNCH
+#undef SOLO_PHYSICS
 #undef SOLO_MARK
   return check_launch(h, "finish_kernel");
 }
@@ -440,20 +539,133 @@ int solo_simulate(SoloHandle h, const float *actions_dev, int32_t broadcast, int
   return SOLO_OK;
 }
 
+// The launches of one env.step, directly into `st`.
+static int step_launches(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev,
+                         float *reward_dev, uint8_t *done_dev, float *terminal_obs_dev, cudaStream_t st) {
+  const int sub = h->K.C.substeps;
+  for (int k = 0; k < sub; k++) {
+    const int last = k == sub - 1;
+    int rc = launch_physics(h, actions_dev, 0, action_scale, last, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+    if (rc) return rc;
+  }
+  return SOLO_OK;
+}
+
+// Capture the step once for this set of output buffers.
+static StepGraph *capture_step(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev,
+                               float *reward_dev, uint8_t *done_dev, float *terminal_obs_dev, cudaStream_t st) {
+  StepGraph *g = new StepGraph();
+  g->graph = nullptr; g->exec = nullptr; g->args = nullptr;
+  const int64_t launches0 = h->launches;
+  cudaError_t e = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
+  if (e != cudaSuccess) { cudaGetLastError(); delete g; return nullptr; }
+  int rc = step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+  e = cudaStreamEndCapture(st, &g->graph);
+  h->launches = launches0;     // nothing ran yet: the replay counts them
+  if (rc || e != cudaSuccess || !g->graph) {
+    cudaGetLastError();
+    if (g->graph) cudaGraphDestroy(g->graph);
+    delete g;
+    return nullptr;
+  }
+  if (cudaGraphInstantiate(&g->exec, g->graph, 0) != cudaSuccess) {
+    cudaGetLastError();
+    cudaGraphDestroy(g->graph);
+    delete g;
+    return nullptr;
+  }
+  // the setup nodes: their action pointer is the one parameter that changes from call to call
+  size_t n_nodes = 0;
+  cudaGraphGetNodes(g->graph, nullptr, &n_nodes);
+  std::vector<cudaGraphNode_t> nodes(n_nodes);
+  cudaGraphGetNodes(g->graph, nodes.data(), &n_nodes);
+  const void *setup_fn = h->ch == 2 ? (const void *)setup_legpar_kernel<2> : (const void *)setup_legpar_kernel<3>;
+  g->args = new SetupArgs();
+  g->args->K = h->K; g->args->B = h->B; g->args->actions = actions_dev; g->args->broadcast = 0;
+  g->args->scale = action_scale;
+  for (cudaGraphNode_t nd : nodes) {
+    cudaGraphNodeType t;
+    if (cudaGraphNodeGetType(nd, &t) != cudaSuccess || t != cudaGraphNodeTypeKernel) continue;
+    cudaKernelNodeParams kp;
+    if (cudaGraphKernelNodeGetParams(nd, &kp) != cudaSuccess) continue;
+    if (kp.func != setup_fn) continue;
+    kp.kernelParams = g->args->ptrs;
+    kp.extra = nullptr;
+    g->setup_nodes.push_back(nd);
+    g->setup_params.push_back(kp);
+  }
+  if ((int)g->setup_nodes.size() != h->K.C.substeps) {   // cannot patch what we cannot find: no graph
+    cudaGetLastError();
+    cudaGraphExecDestroy(g->exec); cudaGraphDestroy(g->graph);
+    delete g->args; delete g;
+    return nullptr;
+  }
+  g->actions = actions_dev; g->scale = action_scale;
+  g->obs = obs_dev; g->reward = reward_dev; g->done = done_dev; g->terminal = terminal_obs_dev;
+  g->epoch = h->epoch; g->used = 0;
+  return g;
+}
+
+static int step_impl(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev, float *reward_dev,
+                     uint8_t *done_dev, float *terminal_obs_dev, cudaStream_t st) {
+  if (!h->use_graph || h->timing) return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+  // retire graphs captured under older bindings / programs
+  if (!h->graphs.empty() && h->graphs[0]->epoch != h->epoch) drop_graphs(h);
+  // the legacy default stream cannot be captured: use a blocking stream of our own, which the
+  // legacy stream orders itself against in both directions
+  cudaStream_t run = st;
+  if (st == nullptr || st == cudaStreamLegacy) {
+    if (!h->gstream && cudaStreamCreate(&h->gstream) != cudaSuccess) {
+      cudaGetLastError();
+      h->use_graph = false;
+      return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+    }
+    run = h->gstream;
+  } else if (st == cudaStreamPerThread) {
+    return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+  }
+  static uint64_t tick = 0;
+  StepGraph *g = nullptr;
+  for (StepGraph *c : h->graphs)
+    if (c->obs == obs_dev && c->reward == reward_dev && c->done == done_dev && c->terminal == terminal_obs_dev &&
+        c->scale == action_scale) { g = c; break; }
+  if (!g) {
+    if (h->graphs.size() >= 8) {   // callers that allocate fresh outputs every step: evict the oldest
+      size_t lru = 0;
+      for (size_t i = 1; i < h->graphs.size(); i++) if (h->graphs[i]->used < h->graphs[lru]->used) lru = i;
+      StepGraph *old = h->graphs[lru];
+      cudaGraphExecDestroy(old->exec); cudaGraphDestroy(old->graph); delete old->args; delete old;
+      h->graphs.erase(h->graphs.begin() + lru);
+    }
+    g = capture_step(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, run);
+    if (!g) {   // capture refused (another capture in flight, ...): plain launches, and stop trying
+      h->use_graph = false;
+      return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
+    }
+    h->graphs.push_back(g);
+  }
+  if (g->actions != actions_dev) {
+    g->args->actions = actions_dev;
+    for (size_t i = 0; i < g->setup_nodes.size(); i++) {
+      cudaError_t e = cudaGraphExecKernelNodeSetParams(g->exec, g->setup_nodes[i], &g->setup_params[i]);
+      if (e != cudaSuccess) return cuda_fail(h, e, "cudaGraphExecKernelNodeSetParams");
+    }
+    g->actions = actions_dev;
+  }
+  g->used = ++tick;
+  cudaError_t e = cudaGraphLaunch(g->exec, run);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaGraphLaunch");
+  h->launches += 3 * (int64_t)h->K.C.substeps;
+  return SOLO_OK;
+}
+
 int solo_step(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev, float *reward_dev,
               uint8_t *done_dev, float *terminal_obs_dev, void *stream) {
   if (!h || !actions_dev || !obs_dev || !reward_dev || !done_dev) return fail(h, SOLO_EINVAL, "null argument");
   if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
   if (!h->program_set || h->obs_dim < 1) return fail(h, SOLO_EINVAL, "no observation program set");
   DeviceGuard g(h->device);
-  const int sub = h->K.C.substeps;
-  for (int k = 0; k < sub; k++) {
-    const int last = k == sub - 1;
-    int rc = launch_physics(h, actions_dev, 0, action_scale, last, obs_dev, reward_dev, done_dev, terminal_obs_dev,
-                            (cudaStream_t)stream);
-    if (rc) return rc;
-  }
-  return SOLO_OK;
+  return step_impl(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, (cudaStream_t)stream);
 }
 
 static int observe_impl(SoloHandle h, float *obs_dev, float *reward_dev, void *stream) {
@@ -490,17 +702,47 @@ int solo_reset(SoloHandle h, const uint8_t *mask_dev, void *stream) {
   return check_launch(h, "reset_kernel");
 }
 
+// Device alias of a host pointer the GPU can reach directly (page-locked memory under unified
+// addressing: cudaHostAlloc / cudaHostRegister, torch's pin_memory()), or null.
+static void *device_alias(const void *host) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
 int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, float *obs_host,
                    float *reward_host, uint8_t *done_host, void *stream) {
   if (!h || !actions_host || !obs_host || !reward_host || !done_host) return fail(h, SOLO_EINVAL, "null argument");
-  if (!h->st_actions) return fail(h, SOLO_EINVAL, "solo_bind_staging has not been called");
+  if (!h->bound) return fail(h, SOLO_EINVAL, "solo_bind has not been called");
+  if (!h->program_set || h->obs_dim < 1) return fail(h, SOLO_EINVAL, "no observation program set");
   DeviceGuard g(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t n = (size_t)h->B.n;
+  // Page-locked caller buffers: the kernels read the actions and write observations / reward /
+  // done THROUGH the caller's own memory (the bytes cross the bus inside the step, overlapped
+  // with the kernels, instead of as separate copies in front of and behind it).  The aliases of
+  // the three result buffers are looked up when the triple changes, the action buffer's on
+  // every call.
+  const void *keys[3] = {obs_host, reward_host, done_host};
+  if (keys[0] != h->map_key[0] || keys[1] != h->map_key[1] || keys[2] != h->map_key[2]) {
+    for (int i = 0; i < 3; i++) { h->map_key[i] = keys[i]; h->map_dev[i] = device_alias(keys[i]); }
+  }
+  void *act_dev = device_alias(actions_host);
+  if (h->zero_copy && act_dev && h->map_dev[0] && h->map_dev[1] && h->map_dev[2]) {
+    int rc = step_impl(h, (const float *)act_dev, action_scale, (float *)h->map_dev[0], (float *)h->map_dev[1],
+                       (uint8_t *)h->map_dev[2], nullptr, st);
+    if (rc) return rc;
+    // (a replay on our own blocking stream is ordered before anything later in the legacy stream)
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return cuda_fail(h, e, "step (asynchronous fault in setup / solve / finish)");
+    return SOLO_OK;
+  }
+  // pageable buffers: through the bound staging buffers
+  if (!h->st_actions) return fail(h, SOLO_EINVAL, "solo_bind_staging has not been called (needed for pageable host buffers)");
   cudaError_t e = cudaMemcpyAsync(h->st_actions, actions_host, n * h->K.M.n_api * sizeof(float),
                                   cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) return cuda_fail(h, e, "H2D actions");
-  int rc = solo_step(h, h->st_actions, action_scale, h->st_obs, h->st_reward, h->st_done, nullptr, stream);
+  int rc = step_launches(h, h->st_actions, action_scale, h->st_obs, h->st_reward, h->st_done, nullptr, st);
   if (rc) return rc;
   const size_t ob = n * h->obs_dim * sizeof(float), rb = n * sizeof(float);
   const bool packed = (char *)h->st_reward == (char *)h->st_obs + ob && (char *)h->st_done == (char *)h->st_reward + rb &&
@@ -516,6 +758,22 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, 
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) return cuda_fail(h, e, "D2H results");
   return SOLO_OK;
+}
+
+int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
+  if (!h) return SOLO_EINVAL;
+  DeviceGuard g(h->device);
+  switch (option) {
+    case SOLO_OPT_GRAPH:
+      h->use_graph = value != 0;
+      if (!h->use_graph) drop_graphs(h);
+      return SOLO_OK;
+    case SOLO_OPT_ZERO_COPY:
+      h->zero_copy = value != 0;
+      return SOLO_OK;
+    default:
+      return fail(h, SOLO_EINVAL, "unknown option");
+  }
 }
 
 int64_t solo_launch_count(SoloHandle h) { return h ? h->launches : 0; }

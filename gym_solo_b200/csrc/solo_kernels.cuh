@@ -209,8 +209,11 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
   float rew = 0.f;
   bool done = false;
   int nan = 0;
+  // programmatic dependent of solve_warp_kernel: the state (last written by the previous step's
+  // finish, which completed before this step's setup started) is fetched while the solver drains
+  if (live) load_state<float, CH, float>(M, B.state + env, B.n, s);
+  cudaGridDependencySynchronize();
   if (live) {
-    load_state<float, CH, float>(M, B.state + env, B.n, s);
     float yb[6], yl[kLegs][CH];
     const float *y = B.yh + env;
 #pragma unroll

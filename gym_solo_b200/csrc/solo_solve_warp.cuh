@@ -365,6 +365,11 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(tl_begin));
 #endif
 
+  // programmatic dependent of setup_legpar_kernel: wait for its records, then let the finish
+  // kernel's blocks be scheduled behind the last solver block
+  cudaGridDependencySynchronize();
+  cudaTriggerProgrammaticLaunchCompletion();
+
   // ---- the environment's record -> smem ----
   {
     const float4 *src = reinterpret_cast<const float4 *>(B.kin + env * KL::kSize);

@@ -3,10 +3,11 @@
 `Solo8VanillaEnv(num_envs=N)` keeps the reference's constructor flags, the
 12-wide action layout (fixed ankle slots ignored), action normalisation, the
 factories, `step -> (obs, reward, done, {'labels': ...})` and `reset -> obs`,
-with a leading num_envs axis on every value.  One `step()` is ONE kernel launch
-(motor rows + physics + observations + reward + terminations) when everything
-registered is a built-in; user-defined plug-ins fall back to a physics launch
-followed by their own torch code.
+with a leading num_envs axis on every value.  One `step()` is one C-ABI call:
+three kernels per physics substep (setup -> solve -> finish; motor rows, physics,
+observations, reward and terminations all inside them), replayed as ONE captured
+CUDA graph when everything registered is a built-in; user-defined plug-ins fall
+back to the physics launches followed by their own torch code.
 """
 from dataclasses import dataclass
 from typing import Any, Dict, Tuple
@@ -59,7 +60,14 @@ class Solo8VanillaEnv(Solo8BaseEnv):
   def __init__(self, use_gui: bool = False, realtime: bool = False,
                config=None, normalize_actions: bool = False,
                normalize_observations: bool = False, num_envs: int = 1,
-               device='cuda:0', auto_reset: bool = False, **kwargs):
+               device='cuda:0', auto_reset: bool = False, output_ring: int = 2, **kwargs):
+    """`output_ring` (batched-only): step() hands out its result tensors from a ring of that
+    many pre-allocated sets (obs, reward, done, terminal observation), so a result stays valid
+    until `output_ring` further steps have been taken and the step replays a captured graph;
+    0 allocates fresh tensors on every step."""
+    self._ring_n = max(0, int(output_ring))
+    self._ring = None
+    self._ring_at = 0
     self._realtime = realtime
     self._normalize = normalize_actions
     self._auto_reset = bool(auto_reset)
@@ -160,11 +168,7 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     plan = self._build_plan()
     if plan is not None:
       c.set_program(plan['program'], token=plan['token'])
-      dev = c.device
-      obs_values = torch.empty((c.n, plan['obs_dim']), dtype=torch.float32, device=dev)
-      reward = torch.empty((c.n,), dtype=torch.float32, device=dev)
-      done = torch.empty((c.n,), dtype=torch.uint8, device=dev)
-      term_obs = torch.empty_like(obs_values) if self._auto_reset else None
+      obs_values, reward, done, term_obs = self._outputs(plan)
       c.step(action, self._scale(), obs_values, reward, done, term_obs)
       if self._realtime:
         time.sleep(self.config.dt)
@@ -195,13 +199,32 @@ class Solo8VanillaEnv(Solo8BaseEnv):
       obs_values = torch.where(done[:, None], fresh, obs_values)
     return obs_values, reward, done, info
 
+  def _outputs(self, plan):
+    c = self.client
+
+    def fresh():
+      dev = c.device
+      o = torch.empty((c.n, plan['obs_dim']), dtype=torch.float32, device=dev)
+      return (o, torch.empty((c.n,), dtype=torch.float32, device=dev),
+              torch.empty((c.n,), dtype=torch.uint8, device=dev),
+              torch.empty_like(o) if self._auto_reset else None)
+    if self._ring_n == 0:
+      return fresh()
+    key = (plan['obs_dim'], self._auto_reset)
+    if self._ring is None or self._ring[0] != key:
+      self._ring = (key, [fresh() for _ in range(self._ring_n)])
+      self._ring_at = 0
+    self._ring_at = (self._ring_at + 1) % self._ring_n
+    return self._ring[1][self._ring_at]
+
   def step_host(self, action: np.ndarray):
     """The reference's calling convention -- numpy in, numpy out -- through the
-    C-ABI's host entry (solo_step_host): H2D of the actions, the fused step,
-    D2H of observations / reward / done, and a stream synchronise.  Needs every
-    registered plug-in to be a built-in.  `action`: a numpy array (staged through a pinned
-    buffer) or a pinned float32 CPU tensor (no staging copy).  The returned arrays alias
-    pinned staging memory and are overwritten by the next call."""
+    C-ABI's host entry (solo_step_host), synchronous.  The kernels read the actions from and
+    write observations / reward / done to page-locked host memory directly (no staging copies:
+    the bytes cross the bus inside the step).  Needs every registered plug-in to be a
+    built-in.  `action`: a numpy array (copied into the env's pinned buffer first) or a pinned
+    float32 CPU tensor (read in place).  The returned arrays alias the env's pinned result
+    block and are overwritten by the next call."""
     plan = self._build_plan()
     if plan is None:
       raise ValueError('step_host needs built-in observations, rewards and terminations')

@@ -214,13 +214,28 @@ int solo_reward(SoloHandle h, float *reward_dev, void *stream);
 int solo_reset(SoloHandle h, const uint8_t *mask_dev, void *stream);
 
 /* Same as solo_step but with HOST buffers (the reference's calling convention:
- * numpy in, numpy out): H2D of actions, the step, D2H of obs/reward/done, and a
- * stream synchronise, through staging buffers bound with solo_bind_staging. */
+ * numpy in, numpy out) and a stream synchronise before it returns.
+ *  - Page-locked buffers (cudaHostAlloc / cudaHostRegister / torch pin_memory();
+ *    all four): the kernels read the actions from and write obs / reward / done
+ *    to the caller's memory directly, so the bytes cross the bus inside the step,
+ *    overlapped with the kernels.  The device aliases of the three result
+ *    buffers are cached while the same three pointers are passed: free or
+ *    unpin them only after passing different ones (or destroying the handle).
+ *  - Pageable buffers: H2D of actions, the step, D2H of obs/reward/done through
+ *    the staging buffers bound with solo_bind_staging. */
 int solo_bind_staging(SoloHandle h, float *actions_dev, float *obs_dev,
                       float *reward_dev, uint8_t *done_dev);
 int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
                    float *obs_host, float *reward_host, uint8_t *done_host,
                    void *stream);
+
+/* Execution options (A/B measurements, debugging); both default to 1.
+ *  SOLO_OPT_GRAPH      solo_step / solo_step_host replay one captured CUDA graph per
+ *                      set of output buffers instead of 3 x num_substeps launches
+ *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies */
+#define SOLO_OPT_GRAPH 1
+#define SOLO_OPT_ZERO_COPY 2
+int solo_set_option(SoloHandle h, int32_t option, int32_t value);
 
 /* Layout of the snapshot buffer bound with solo_bind: per_env = 0 (default) one
  * reset state float[state_dim] shared by every environment -- the reference's

@@ -301,6 +301,53 @@ def test_step_host_matches_device_step():
     assert np.array_equal(o1.cpu().numpy(), o2)
     assert np.array_equal(r1.cpu().numpy(), r2)
     assert np.array_equal(d1.cpu().numpy(), d2)
+  # every execution variant gives the same bits: captured graph vs plain launches, zero-copy
+  # through pinned memory vs staged copies, and pageable host buffers through the C-ABI
+  from gym_solo_b200 import _abi as abi
+  c = b_env.client
+  for graph, zero_copy in ((0, 1), (1, 0), (0, 0), (1, 1)):
+    c.set_option(abi.OPT_GRAPH, graph)
+    c.set_option(abi.OPT_ZERO_COPY, zero_copy)
+    a_env.client.set_option(abi.OPT_GRAPH, graph)
+    for _ in range(2):
+      act = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12)).astype(np.float32)
+      o1, r1, d1, _ = a_env.step(torch.tensor(act, device='cuda:0'))
+      o2, r2, d2, _ = b_env.step_host(act)
+      assert np.array_equal(o1.cpu().numpy(), o2), (graph, zero_copy)
+      assert np.array_equal(r1.cpu().numpy(), r2) and np.array_equal(d1.cpu().numpy(), d2)
+  act = rng.uniform(-2 * np.pi, 2 * np.pi, (n, 12)).astype(np.float32)       # pageable numpy memory
+  o_np, r_np, d_np = np.zeros((n, 21), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8)
+  o1, r1, d1, _ = a_env.step(torch.tensor(act, device='cuda:0'))
+  c.step_host(act, 1.0, o_np, r_np, d_np)
+  assert np.array_equal(o1.cpu().numpy(), o_np) and np.array_equal(r1.cpu().numpy(), r_np)
+  assert np.array_equal(d1.cpu().numpy(), d_np)
+  # results of consecutive steps come from a ring of two output sets: the previous one is intact
+  act = torch.tensor(rng.uniform(-1, 1, (n, 12)).astype(np.float32), device='cuda:0')
+  o_a, _, _, _ = a_env.step(act)
+  keep = o_a.clone()
+  o_b, _, _, _ = a_env.step(act)
+  assert o_b.data_ptr() != o_a.data_ptr() and torch.equal(o_a, keep)
+  a_env.close(); b_env.close()
+
+
+def test_step_on_a_side_stream_and_launch_count():
+  """The step captured and replayed on a caller stream (torch.cuda.stream): same bits as the
+  default stream; launch_count() counts the kernels of the replayed graphs."""
+  n = 100
+  a_env, b_env = _env(n, False, 1000), _env(n, False, 1000)
+  a_env.reset(); b_env.reset()
+  side = torch.cuda.Stream()
+  g = torch.Generator(device='cuda:0').manual_seed(61)
+  l0 = b_env.client.launch_count()
+  for _ in range(6):
+    act = (torch.rand((n, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    o1, r1, d1, _ = a_env.step(act)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+      o2, r2, d2, _ = b_env.step(act)
+    torch.cuda.current_stream().wait_stream(side)
+    assert torch.equal(o1, o2) and torch.equal(r1, r2) and torch.equal(d1, d2)
+  assert b_env.client.launch_count() - l0 == 18
   a_env.close(); b_env.close()
 
 
