@@ -76,6 +76,7 @@ class SoloConfig(C.Structure):
       ('contact_breaking_threshold', C.c_double),
       ('max_coordinate_velocity', C.c_double),
       ('residual_threshold', C.c_double),
+      ('joint_limit_erp', C.c_double), ('joint_limit_max_impulse', C.c_double),
       ('solver_iterations', C.c_int32), ('num_substeps', C.c_int32),
       ('control_mode', C.c_int32), ('max_contacts', C.c_int32),
   ]
@@ -232,6 +233,8 @@ def make_config(dt=1e-3, gravity=(0., 0., -9.81), motor_torque_limit=2.,
   c.contact_breaking_threshold = kw.get('contact_breaking_threshold', 0.02)
   c.max_coordinate_velocity = kw.get('max_coordinate_velocity', 100.0)
   c.residual_threshold = kw.get('residual_threshold', 1e-7)
+  c.joint_limit_erp = kw.get('joint_limit_erp', 0.2)
+  c.joint_limit_max_impulse = kw.get('joint_limit_max_impulse', 100.0)
   c.solver_iterations = solver_iterations
   c.num_substeps = num_substeps
   c.control_mode = control_mode

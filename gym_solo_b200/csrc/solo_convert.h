@@ -91,6 +91,8 @@ inline std::string convert_config(const SoloConfig &c, ConfigT<T> *out) {
   o.kp = (T)c.motor_kp; o.kd = (T)c.motor_kd;
   o.erp = (T)c.contact_erp; o.slop = (T)c.contact_slop; o.breaking = (T)c.contact_breaking_threshold;
   o.max_vel = (T)c.max_coordinate_velocity; o.res_thr = (T)c.residual_threshold;
+  if (!(c.joint_limit_erp >= 0) || !(c.joint_limit_max_impulse >= 0)) return "bad joint limit parameters";
+  o.lim_erp = (T)c.joint_limit_erp; o.lim_max = (T)c.joint_limit_max_impulse;
   o.iters = c.solver_iterations; o.substeps = c.num_substeps > 0 ? c.num_substeps : 1;
   o.control_mode = c.control_mode; o.max_contacts = c.max_contacts;
   return "";

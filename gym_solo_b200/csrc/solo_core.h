@@ -78,6 +78,7 @@ struct ConfigT {
   T gravity[3];
   T torque_limit, lin_damp, ang_damp;
   T kp, kd, erp, slop, breaking, max_vel, res_thr;
+  T lim_erp, lim_max;                // joint-limit rows: positional correction, impulse cap
   int32_t iters, substeps, control_mode, max_contacts;
 };
 
@@ -220,6 +221,19 @@ template <typename T> SOLO_HD M3<T> axis_angle(V3<T> a, T th) {
   R.m[3] = t * a.x * a.y + s * a.z; R.m[4] = t * a.y * a.y + c;       R.m[5] = t * a.y * a.z - s * a.x;
   R.m[6] = t * a.x * a.z - s * a.y; R.m[7] = t * a.y * a.z + s * a.x; R.m[8] = t * a.z * a.z + c;
   return R;
+}
+
+// Joint limit of one dof (URDF <limit lower upper>, solo.urdf:47; Bullet's
+// btMultiBodyJointLimitConstraint): its row exists only while the limit is reached or
+// violated.  Returns 0 (no row), +1 (lower limit, *pen = q - lower <= 0) or -1 (upper limit,
+// *pen = upper - q <= 0).  lower > upper means "no limit" (continuous joint).
+template <typename T> SOLO_HD int joint_limit_state(const T q, const T lower, const T upper, T *pen) {
+  *pen = 0;
+  if (!(lower <= upper)) return 0;
+  const T lo = q - lower, hi = upper - q;
+  if (lo <= 0) { *pen = lo; return 1; }
+  if (hi <= 0) { *pen = hi; return -1; }
+  return 0;
 }
 
 // ---- per-environment state (registers) ---------------------------------------

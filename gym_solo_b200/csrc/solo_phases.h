@@ -39,8 +39,14 @@ namespace solo {
 //   kS   s  = |T J^T|        (true impulse = lambda' / s; Bullet residual = delta' * s)
 //   kIs  1 / s
 //   kX   normal row: contact candidate index (as float); first friction row:
-//        mu / s_normal (friction limit = kX * lambda'_normal in true units)
+//        mu / s_normal (friction limit = kX * lambda'_normal in true units);
+//        motor slot: b' of the joint-limit row of the same joint (it shares the
+//        motor row's u up to its sign, see `lim` below)
 // Slots: kLegs * CH motor rows (leg major), then per contact: normal, t1, t2.
+//
+// Joint-limit rows (btMultiBodyJointLimitConstraint): J = dir e_j with dir = +1 at the
+// lower and -1 at the upper limit, i.e. u_limit = dir * u_motor.  Which slots have a live
+// limit row is a bit mask `lim`: bit j = slot j has one, bit 16 + j = it is the upper one.
 template <int CH> struct RowLayout {
   static constexpr int kJ = 6 + CH;
   static constexpr int kB = kJ, kS = kJ + 1, kIs = kJ + 2, kX = kJ + 3;
@@ -76,13 +82,15 @@ template <int CH> struct KinLayout {
   static constexpr int kVl = kBh + CH * 6;                                   // CH
   static constexpr int kJoint = kVl + CH;                                    // per joint: axis 3, origin 3, rotation 9
   static constexpr int kLegSize = kJoint + CH * 15;
-  static constexpr int kSize = (kLeg + kLegs * kLegSize + 3) & ~3;           // 328 (CH 2), 524 (CH 3)
+  static constexpr int kLim = kLeg + kLegs * kLegSize;                       // 1: joint-limit mask (bits of a float)
+  static constexpr int kSize = (kLim + 1 + 3) & ~3;                          // 328 (CH 2), 524 (CH 3)
 };
 
 // Per-env header: contact-group ends (base, leg 0..3), 8 bits each.
 struct RowHeader {
   uint32_t ends03;   // leg_end[0..3]
   uint32_t nc;       // leg_end[4] = number of contacts
+  uint32_t lim;      // live joint-limit rows (see RowLayout)
 };
 
 SOLO_HD int lowest_bit(uint32_t m) {

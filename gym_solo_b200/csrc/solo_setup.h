@@ -280,7 +280,8 @@ SOLO_LEG_LOOP
   }
 
   // whiten g (base part, pre-Ls) + leg part already in o[6..], normalise, store
-  auto finish_row = [&](T (&o)[RL::kRow], const T (&g)[6], T den_leg, T verr, T extra, T *dst) {
+  auto finish_row = [&](T (&o)[RL::kRow], const T (&g)[6], T den_leg, T verr, T extra, T *dst,
+                        const bool scale_extra = false) {
     T den = den_leg;
 #pragma unroll
     for (int a = 0; a < 6; a++) {
@@ -294,22 +295,33 @@ SOLO_LEG_LOOP
     const T is = T(1) / sn;
 #pragma unroll
     for (int a = 0; a < RL::kJ; a++) o[a] *= is;
-    o[RL::kB] = verr * is; o[RL::kS] = sn; o[RL::kIs] = is; o[RL::kX] = extra;
+    o[RL::kB] = verr * is; o[RL::kS] = sn; o[RL::kIs] = is; o[RL::kX] = scale_extra ? extra * is : extra;
 #pragma unroll
     for (int a = RL::kX + 1; a < RL::kRow; a++) o[a] = 0;
     store_row(dst, o);
     return is;
   };
 
-  // ---------------- motor rows (POSITION_CONTROL) ----------------
+  // ---------------- motor rows (POSITION_CONTROL) and joint-limit rows ----------------
+  // A joint at or beyond a URDF limit gets Bullet's unilateral limit row; it shares the motor
+  // row's whitened direction (J = +-e_j), so the slot is built whenever either row is live.
   const bool motors = (C.control_mode == 0);
+  uint32_t lim_bits = 0;
 SOLO_LEG_LOOP
   for (int l = 0; l < kLegs; l++)
 #pragma unroll
     for (int i = 0; i < CH; i++) {
       T o[RL::kRow];
       T *dst = rows + (int64_t)(l * CH + i) * slot_stride;
-      const bool act = motors && (l < M.n_legs) && (i < M.chain_len[l]);
+      const bool on = (l < M.n_legs) && (i < M.chain_len[l]);
+      T pen = 0;
+      int ldir = 0;
+      if (on) {
+        const int api = M.dof_api[M.dof0[l] + i];
+        ldir = joint_limit_state(s.q[l][i], M.api_lower[api], M.api_upper[api], &pen);
+      }
+      if (ldir != 0) lim_bits |= (1u << (l * CH + i)) | (ldir < 0 ? (1u << (16 + l * CH + i)) : 0u);
+      const bool act = on && (motors || ldir != 0);
       if (act) {
         T g[6] = {0, 0, 0, 0, 0, 0};
         T den = 0;
@@ -322,8 +334,10 @@ SOLO_LEG_LOOP
           for (int a = 0; a < 6; a++) g[a] -= Bh[l][k][a] * e;
         }
         // btMultiBodyJointMotor: velocity error kp (q* - q)/dt - kd v
-        const T verr = C.kp * (cmd[l][i] - s.q[l][i]) * C.inv_dt - C.kd * vl[l][i];
-        finish_row(o, g, den, verr, T(0), dst);
+        const T verr = motors ? C.kp * (cmd[l][i] - s.q[l][i]) * C.inv_dt - C.kd * vl[l][i] : T(0);
+        // limit row (along dir e_j): positional correction -pen erp / dt, velocity error -dir v
+        const T lerr = ldir != 0 ? -pen * C.lim_erp * C.inv_dt - (T)ldir * vl[l][i] : T(0);
+        finish_row(o, g, den, verr, lerr, dst, true);
       } else {
 #pragma unroll
         for (int a = 0; a < RL::kRow; a++) o[a] = 0;
@@ -367,8 +381,11 @@ SOLO_LEG_LOOP
         for (int i = 0; i < 9; i++) kj[6 + i] = jR[l][j].m[i];
       }
     }
+    union { uint32_t u; float f; } lim_word;   // the mask travels as the bits of one float of the record
+    lim_word.u = lim_bits;
+    kin[KL::kLim] = (T)lim_word.f;
     RowHeader h0;
-    h0.ends03 = 0; h0.nc = 0;
+    h0.ends03 = 0; h0.nc = 0; h0.lim = lim_bits;
     return h0;
   }
 
@@ -470,6 +487,7 @@ SOLO_LEG_LOOP
   RowHeader h;
   h.ends03 = ends03;
   h.nc = (uint32_t)nc;
+  h.lim = lim_bits;
   return h;
 }
 

@@ -292,6 +292,22 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
       vl[i] = m_clamp(qd[i] + acc * dt, -C.max_vel, C.max_vel);
     }
   }
+  // ---- joint limits of the own leg; the environment's mask is the OR over the four lanes ----
+  T lpen[CH];
+  int ldir[CH];
+  uint32_t lim_bits = 0;
+#pragma unroll
+  for (int i = 0; i < CH; i++) {
+    lpen[i] = 0.f;
+    ldir[i] = 0;
+    if (act[i]) {
+      const int api = M.dof_api[M.dof0[l] + i];
+      ldir[i] = joint_limit_state(q[i], M.api_lower[api], M.api_upper[api], &lpen[i]);
+    }
+    if (ldir[i] != 0) lim_bits |= (1u << (l * CH + i)) | (ldir[i] < 0 ? (1u << (16 + l * CH + i)) : 0u);
+  }
+  lim_bits |= __shfl_xor_sync(0xffffffffu, lim_bits, 1);
+  lim_bits |= __shfl_xor_sync(0xffffffffu, lim_bits, 2);
   if (!live) return;
 
   // ---- factors for finish_step (FactorLayout) ----
@@ -320,14 +336,16 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
     for (int i = 0; i < CH; i++) fac[(FL::kVl + l * CH + i) * fs] = vl[i];
   }
 
-  // ---- motor rows of the own leg (POSITION_CONTROL) ----
+  // ---- motor rows of the own leg (POSITION_CONTROL) and joint-limit rows ----
+  // a joint at or beyond a URDF limit gets Bullet's unilateral limit row; it shares the motor
+  // row's whitened direction (J = +-e_j), so the slot is built whenever either row is live
   float *kin = B.kin + env * KL::kSize;
   const bool motors = (C.control_mode == 0);
 #pragma unroll
   for (int i = 0; i < CH; i++) {
     T o[RL::kRow];
     float *dst = kin + KL::kMotor + (l * CH + i) * RL::kRow;
-    if (motors && act[i]) {
+    if (act[i] && (motors || ldir[i] != 0)) {
       T g[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       T den = 0.f;
 #pragma unroll
@@ -339,7 +357,9 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
         for (int a = 0; a < 6; a++) g[a] -= Bh[k][a] * e;
       }
       // btMultiBodyJointMotor: velocity error kp (q* - q)/dt - kd v
-      const T verr = C.kp * (cmd[i] - q[i]) * C.inv_dt - C.kd * vl[i];
+      const T verr = motors ? C.kp * (cmd[i] - q[i]) * C.inv_dt - C.kd * vl[i] : 0.f;
+      // limit row (along dir e_j): positional correction -pen erp / dt, velocity error -dir v
+      const T lerr = ldir[i] != 0 ? -lpen[i] * C.lim_erp * C.inv_dt - (T)ldir[i] * vl[i] : 0.f;
 #pragma unroll
       for (int a = 0; a < 6; a++) {
         T t = 0.f;
@@ -352,7 +372,7 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
       const T is = 1.f / sn;
 #pragma unroll
       for (int a = 0; a < RL::kJ; a++) o[a] *= is;
-      o[RL::kB] = verr * is; o[RL::kS] = sn; o[RL::kIs] = is; o[RL::kX] = 0.f;
+      o[RL::kB] = verr * is; o[RL::kS] = sn; o[RL::kIs] = is; o[RL::kX] = lerr * is;
 #pragma unroll
       for (int a = RL::kX + 1; a < RL::kRow; a++) o[a] = 0.f;
     } else {
@@ -375,6 +395,7 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
     kin[KL::kO0] = o0.x; kin[KL::kO0 + 1] = o0.y; kin[KL::kO0 + 2] = o0.z;
 #pragma unroll
     for (int i = 0; i < 9; i++) kin[KL::kR0 + i] = R0.m[i];
+    kin[KL::kLim] = __uint_as_float(lim_bits);
   }
   {
     float *kl = kin + KL::kLeg + l * KL::kLegSize;

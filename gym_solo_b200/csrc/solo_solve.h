@@ -1,8 +1,10 @@
 // solo_solve.h -- phase 2 of the physics step (see solo_phases.h): projected
 // Gauss-Seidel over the whitened, normalised rows, in the order of
 // btMultiBodyConstraintSolver::solveSingleIteration (Bullet
-// recollection): motor rows (direction of traversal alternates with iteration
-// parity), then every contact normal row, then every friction pair (both rows
+// recollection): the non-contact rows -- joint-limit rows (created at URDF import,
+// one per joint at or beyond a limit), then the motor rows, the traversal of the
+// whole list alternating in direction with iteration parity -- then every contact
+// normal row, then every friction pair (both rows
 // evaluated on the same velocity, radial projection onto the disc of radius
 // mu * lambda_n: resolveConeFrictionConstraintRows); early exit once the
 // largest squared Bullet residual of an iteration is <= res_thr.
@@ -37,7 +39,11 @@ SOLO_HD int solve_rows(const ConfigT<T> &C, const uint32_t motor_mask, const T *
 #pragma unroll
   for (int j = 0; j < kLegs * CH; j++) mlam[j] = 0;
   for (int r = 0; r < 3 * nc; r++) lam[(int64_t)r * lam_stride] = 0;
-  if (motor_mask == 0 && nc == 0) return 0;
+  const uint32_t lim = h.lim;
+  T llam[kLegs * CH];      // scaled joint-limit impulses (>= 0 along the row's own direction)
+#pragma unroll
+  for (int j = 0; j < kLegs * CH; j++) llam[j] = 0;
+  if (motor_mask == 0 && nc == 0 && lim == 0) return 0;
 
   const T mlim = C.torque_limit * C.dt;
   const T *crow = rows + (int64_t)RL::kMotorSlots * slot_stride;
@@ -57,6 +63,33 @@ SOLO_HD int solve_rows(const ConfigT<T> &C, const uint32_t motor_mask, const T *
   int it = 0;
   for (; it < C.iters;) {
     T res = 0;
+    // joint-limit rows: u = dir * u_motor of the slot, b' in its kX, 0 <= lambda' <= lim_max * s
+    auto limit = [&](const int l, const int i) {
+      const int j = l * CH + i;
+      if (((lim >> j) & 1u) == 0) return;
+      T r[RL::kRow];
+      load_row(rows + (int64_t)j * slot_stride, r);
+      const T dir = ((lim >> (16 + j)) & 1u) ? T(-1) : T(1);
+      T dotv = 0;
+#pragma unroll
+      for (int a = 0; a < 6; a++) dotv += r[a] * yb[a];
+#pragma unroll
+      for (int k = 0; k < CH; k++) dotv += r[6 + k] * yl[l][k];
+      const T old = llam[j];
+      const T sum = m_clamp(old + (r[RL::kX] - dir * dotv), T(0), C.lim_max * r[RL::kS]);
+      const T d = (sum - old) * dir;
+      llam[j] = sum;
+#pragma unroll
+      for (int a = 0; a < 6; a++) yb[a] += r[a] * d;
+#pragma unroll
+      for (int k = 0; k < CH; k++) yl[l][k] += r[6 + k] * d;
+      const T rr = d * r[RL::kS];
+      res = m_max(res, rr * rr);
+    };
+    if (lim != 0 && (it & 1)) {
+#pragma unroll
+      for (int jj = 0; jj < kLegs * CH; jj++) limit(jj / CH, jj % CH);
+    }
     if (motor_mask != 0) {
       auto motor = [&](const int l, const int i) {
         // dead slots (shorter chains, torque mode) hold all-zero rows: no test needed
@@ -87,6 +120,10 @@ SOLO_HD int solve_rows(const ConfigT<T> &C, const uint32_t motor_mask, const T *
 #pragma unroll
         for (int jj = kLegs * CH - 1; jj >= 0; jj--) motor(jj / CH, jj % CH);
       }
+    }
+    if (lim != 0 && !(it & 1)) {
+#pragma unroll
+      for (int jj = kLegs * CH - 1; jj >= 0; jj--) limit(jj / CH, jj % CH);
     }
 
     // ---- normal rows ----

@@ -49,6 +49,7 @@ struct WarpSolveSmem {
   float kin[KinLayout<CH>::kSize];                   // setup_kernel's record (motor rows first)
   float ent[kMaxContacts][ActiveLayout<CH>::kSize];  // active contacts, sorted by contact index
   int32_t list[kMaxContacts];                        // contact -> support point
+  float llam[kLegs * CH];                            // scaled joint-limit impulses (rows are rare)
 };
 
 // contact bitmasks: 32 bits when the env has <= 32 contacts (99.8 % of env-steps), else 64
@@ -134,7 +135,7 @@ __device__ __noinline__ void build_entry(float *e, const float *kin, const Confi
 template <int CH, int NR>
 __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH> &sm, const float margin,
                                           const float *cand_tab, const float link_mu, const uint32_t motor_mask,
-                                          const int nc, const int lane, float (&y)[6 + kLegs * CH],
+                                          const uint32_t lim, const int nc, const int lane, float (&y)[6 + kLegs * CH],
                                           float (&mlam)[kLegs * CH], int *n_active) {
   typedef RowLayout<CH> RL;
   typedef KinLayout<CH> KL;
@@ -182,8 +183,47 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
 #ifdef SOLO_IDLE_PROBE
   int probe_visits = 0, probe_idle = 0;   // probe build: how many promoted-contact visits found the contact idle
 #endif
+  // Joint-limit rows (btMultiBodyJointLimitConstraint; a joint at or beyond a URDF limit).  They
+  // sit in front of the motor rows in Bullet's non-contact list, whose traversal alternates
+  // with iteration parity.  u = dir * u_motor of the slot (expanded to the dense width with
+  // selects: yh stays in registers), b' in the slot's kX, 0 <= lambda' <= lim_max * s.  Rare,
+  // so one rolled loop: nothing of it is on the path of an environment without limit rows.
+  auto limit_rows = [&](const bool forward, float &res) {
+#pragma unroll 1
+    for (int jj = 0; jj < kLegs * CH; jj++) {
+      const int j = forward ? jj : kLegs * CH - 1 - jj;
+      if (((lim >> j) & 1u) == 0) continue;
+      const int l = j / CH;
+      float r[RL::kRow];
+      load_row(sm.kin + KL::kMotor + j * RL::kRow, r);
+      const float dir = ((lim >> (16 + j)) & 1u) ? -1.f : 1.f;
+      float dotv = 0.f;
+#pragma unroll
+      for (int a = 0; a < 6; a++) dotv = fmaf(r[a], y[a], dotv);
+#pragma unroll
+      for (int l2 = 0; l2 < kLegs; l2++)
+#pragma unroll
+        for (int k = 0; k < CH; k++) dotv = fmaf(l2 == l ? r[6 + k] : 0.f, y[6 + l2 * CH + k], dotv);
+      const float old = sm.llam[j];
+      const float sum = fminf(fmaxf(old + (r[RL::kX] - dir * dotv), 0.f), C.lim_max * r[RL::kS]);
+      const float d = (sum - old) * dir;
+      __syncwarp();
+      if (lane == 0) sm.llam[j] = sum;
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < 6; a++) y[a] = fmaf(r[a], d, y[a]);
+#pragma unroll
+      for (int l2 = 0; l2 < kLegs; l2++)
+#pragma unroll
+        for (int k = 0; k < CH; k++) y[6 + l2 * CH + k] = fmaf(l2 == l ? r[6 + k] : 0.f, d, y[6 + l2 * CH + k]);
+      const float rr = d * r[RL::kS];
+      res = fmaxf(res, rr * rr);
+      budget -= fabsf(d);
+    }
+  };
   for (; it < C.iters;) {
     float res = 0.f;
+    if (lim != 0 && (it & 1)) limit_rows(true, res);
     // ---- motor rows (btMultiBodyJointMotor), direction alternates with parity ----
     if (motor_mask != 0) {
       auto motor = [&](const int l, const int i) {
@@ -220,6 +260,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         for (int jj = kLegs * CH - 1; jj >= 0; jj--) motor(jj / CH, jj % CH);
       }
     }
+    if (lim != 0 && !(it & 1)) limit_rows(false, res);
 
     if (nc > 0) {
       // ---- normal rows ----
@@ -404,10 +445,13 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
 
   float y[W], mlam[kLegs * CH];
   int it = 0, n_active = 0;
-  if (motor_mask != 0 || nc > 0) {
+  const uint32_t lim = __float_as_uint(sm.kin[KL::kLim]);   // live joint-limit rows (setup)
+  if (lane < kLegs * CH) sm.llam[lane] = 0.f;
+  __syncwarp();
+  if (motor_mask != 0 || nc > 0 || lim != 0) {
     const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
-    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, nc, lane, y, mlam, &n_active);
-    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, nc, lane, y, mlam, &n_active);
+    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
   } else {
 #pragma unroll
     for (int a = 0; a < W; a++) y[a] = 0.f;

@@ -77,6 +77,9 @@ typedef struct SoloConfig {
   double contact_breaking_threshold; /* 0.02 */
   double max_coordinate_velocity; /* btMultiBody m_maxCoordinateVelocity = 100 */
   double residual_threshold;      /* m_leastSquaresResidualThreshold = 1e-7 */
+  double joint_limit_erp;         /* btMultiBodyJointLimitConstraint rows (URDF limits, solo.urdf:47):
+                                     positional correction, m_erp = 0.2 */
+  double joint_limit_max_impulse; /* btMultiBodyConstraint m_maxAppliedImpulse = 100 */
   int32_t solver_iterations;      /* 50 */
   int32_t num_substeps;           /* physics steps of dt per action (reference: 1) */
   int32_t control_mode;           /* 0 = POSITION_CONTROL, 1 = torque */

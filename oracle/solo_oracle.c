@@ -18,8 +18,13 @@
  *   B4 hull(+1 mm margin) vs ground, normal row (erp2 .08, slop 1e-5,
  *      speculative rows inside the 2 cm breaking threshold) + two friction
  *      rows (btPlaneSpace1 directions) with the implicit friction cone
- *   B6 iteration order: motor rows (direction alternates with iteration
- *      parity), normal rows, friction pairs; early exit on residual^2 <= 1e-7
+ *   B6 iteration order: non-contact rows (joint-limit rows, then motor rows;
+ *      direction of traversal alternates with iteration parity), normal rows,
+ *      friction pairs; early exit on residual^2 <= 1e-7
+ *   joint limits (URDF <limit lower upper>, solo.urdf:47) =
+ *      btMultiBodyJointLimitConstraint, created at import before the motors: one
+ *      unilateral row J = +-e_j per joint at or beyond a limit, 0 <= lambda <= 100,
+ *      rhs = -pen * erp / dt - rel_vel with erp = m_erp = 0.2
  * Deliberately written with DIFFERENT algorithms from the CUDA kernel so the
  * two check each other: Featherstone ABA in world Plucker coordinates, a dense
  * Jacobian-built mass matrix + Cholesky for M^-1 J^T, and dense (6+ndof)-wide
@@ -475,6 +480,29 @@ static int physics_step(const SoloModel *m, const SoloConfig *cfg, double *st, c
   mass_matrix(m, &k, M);
   if (cholesky(n, M)) { free(M); free(ct); return -2; }
   int n_motor = (cfg->control_mode == SOLO_CONTROL_POSITION) ? nd : 0;
+  /* joint-limit rows first (the constraints exist since URDF import; a row is emitted only
+   * while q is at or beyond the limit: createConstraintRows skips penetration > 0) */
+  Row *limr = (Row *)calloc((size_t)SOLO_MAX_DOF + 1, sizeof(Row));
+  int n_lim = 0;
+  {
+    int dof_api[SOLO_MAX_DOF];
+    for (int j = 0; j < m->n_api; j++)
+      if (m->api_dof[j] >= 0) dof_api[m->api_dof[j]] = j;
+    for (int d = 0; d < nd; d++) {
+      double lower = m->api_lower[dof_api[d]], upper = m->api_upper[dof_api[d]];
+      if (!(lower <= upper)) continue;
+      double dir = 0, pen = 0;
+      if (q[d] - lower <= 0) { dir = 1; pen = q[d] - lower; }
+      else if (upper - q[d] <= 0) { dir = -1; pen = upper - q[d]; }
+      if (dir == 0) continue;
+      Row *r = &limr[n_lim++];
+      r->J[6 + d] = dir;
+      fill_row(n, M, r);
+      double rel = dir * v[6 + d];
+      r->rhs = (-pen * cfg->joint_limit_erp / dt - rel) * r->dinv;
+      r->lo = 0; r->hi = cfg->joint_limit_max_impulse;
+    }
+  }
   Row *motor = (Row *)calloc((size_t)SOLO_MAX_DOF + 1, sizeof(Row));
   Row *nrm = (Row *)calloc((size_t)SOLO_MAX_CAND + 1, sizeof(Row));
   Row *fr = (Row *)calloc(2 * (size_t)SOLO_MAX_CAND + 1, sizeof(Row));
@@ -516,9 +544,9 @@ static int physics_step(const SoloModel *m, const SoloConfig *cfg, double *st, c
   int it;
   for (it = 0; it < cfg->solver_iterations; it++) {
     double res = 0, r, r2;
-    for (int j = 0; j < n_motor; j++) {
-      int idx = (it & 1) ? j : n_motor - 1 - j;
-      r = resolve_row(n, &motor[idx], dv); if (r * r > res) res = r * r;
+    for (int j = 0; j < n_lim + n_motor; j++) {
+      int idx = (it & 1) ? j : n_lim + n_motor - 1 - j;
+      r = resolve_row(n, idx < n_lim ? &limr[idx] : &motor[idx - n_lim], dv); if (r * r > res) res = r * r;
     }
     for (int j = 0; j < nc; j++) { r = resolve_row(n, &nrm[j], dv); if (r * r > res) res = r * r; }
     for (int j = 0; j < nc; j++) {
@@ -537,7 +565,7 @@ static int physics_step(const SoloModel *m, const SoloConfig *cfg, double *st, c
     for (int i = 0; i < nc; i++) diag->normal_force[ct[i].cand] = nrm[i].lambda / dt;
     for (int d = 0; d < SOLO_MAX_DOF; d++) diag->motor_torque[d] = d < n_motor ? motor[d].lambda / dt : 0;
   }
-  free(M); free(motor); free(nrm); free(fr); free(ct);
+  free(M); free(limr); free(motor); free(nrm); free(fr); free(ct);
 
   /* 5. integrate positions with the new velocities (stepPositionsMultiDof) */
   for (int i = 0; i < 3; i++) pos[i] += dt * v[i];

@@ -71,12 +71,22 @@ def test_torque_mode_and_free_flight(world):
   s[2] += 0.5          # airborne: no contacts, no motor rows -> zero PGS iterations
   act = np.zeros(12)
   act[[0, 1, 3, 4]] = [0.5, -0.3, 1.0, 2.5]     # 2.5 > limit 2 -> clamped
-  for _ in range(20):
+  limited = 0
+  for _ in range(50):       # (the robot lands after ~55 steps)
     want = orc.step(s, act)
     got, d = H.hostsim_step(model, cfg, s, act, use_double=True)
-    assert d['n_contacts'] == 0 and d['iterations'] == 0
+    assert d['n_contacts'] == 0
+    if np.abs(s[13:21]).max() < 10.0:
+      assert d['iterations'] == 0       # no rows at all
+    else:
+      # the undamped legs reach the URDF limit (+-10 rad, solo.urdf:47) within a few dozen steps:
+      # joint-limit rows, the only rows of this solve
+      assert d['iterations'] >= 1
+      limited += 1
     np.testing.assert_allclose(got, want, atol=1e-10)
     s = want
+  assert limited > 10
+  assert np.abs(s[13:21]).max() < 10.5   # held at the limit, not running away at 100 rad/s
 
 
 @pytest.mark.parametrize('name', ['solo8_mmr_v4', 'solo8_urdf_v3'])
@@ -98,3 +108,36 @@ def test_mmr_v4_model_float64_core_tracks_oracle(name):
     worst = max(worst, np.abs(a - c).max())
   assert worst < 1e-9, worst
   assert max(its) > 10
+
+
+def test_mmr_v4_float32_core_and_where_its_error_comes_from():
+  """The few-gram distal links of the MMR v4 model in float32 (the arithmetic of the CUDA path):
+  leg blocks formed about the joints' own origins keep the per-step joint-rate error at the
+  1e-3 level on resting multi-contact states (round 1: 2e-2); the splice runs show that the
+  mass-matrix factors are no longer the source (any float32 input of the non-converged
+  28-contact solve gives the same ~1e-3)."""
+  import ctypes as C
+  blob, model, config = H.model_and_config('solo8_mmr_v4', dt=1 / 240.)
+  orc = H.oracle(model, config)
+  lib = H.hostsim()
+  rng = np.random.RandomState(12)
+  s = orc.initial_state()
+  pool = []
+  for k in range(330):
+    s = orc.step(s, np.zeros(10) if k < 200 or k % 15 else rng.uniform(-2 * np.pi, 2 * np.pi, 10))
+    if k % 5 == 0:
+      pool.append(s.copy())
+  worst, worst_fac = 0.0, 0.0
+  for s in pool:
+    s32 = s.astype(np.float32).astype(np.float64)
+    a32 = rng.uniform(-2 * np.pi, 2 * np.pi, 10).astype(np.float32).astype(np.float64)
+    want = orc.step(s32, a32)
+    got, _ = H.hostsim_step(model, config, s32, a32, use_double=False)
+    worst = max(worst, np.abs(got - want)[23:].max())
+    st = s32.copy()
+    rc = lib.hostsim_step_splice(C.byref(model), C.byref(config), 2, st.ctypes.data_as(C.POINTER(C.c_double)),
+                                 a32.ctypes.data_as(C.POINTER(C.c_double)))
+    if rc == 0:
+      worst_fac = max(worst_fac, np.abs(st - want)[23:].max())
+  assert worst <= 4e-3, worst
+  assert worst_fac <= 5e-4, worst_fac       # float32 factors (Ls, Bh, E) in a float64 step

