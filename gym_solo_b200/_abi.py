@@ -13,6 +13,7 @@ MAX_DOF = 12
 MAX_BODIES = 13
 MAX_API = 16
 MAX_CAND = 128
+MAX_CONTACTS = 56
 MAX_OBS_TERMS = 8
 MAX_REWARD_OPS = 32
 MAX_TERM_TERMS = 8
@@ -36,6 +37,7 @@ REW_MUL = 17
 
 OPT_GRAPH = 1
 OPT_ZERO_COPY = 2
+OPT_SOLVER_OCCUPANCY = 3
 
 TERM_PERPETUAL = 1
 TERM_TIME = 2
@@ -214,7 +216,7 @@ def make_model(blob, link_friction=None):
 
 def make_config(dt=1e-3, gravity=(0., 0., -9.81), motor_torque_limit=2.,
                 linear_damping=.04, angular_damping=.04, num_substeps=1,
-                control_mode=CONTROL_POSITION, max_contacts=64,
+                control_mode=CONTROL_POSITION, max_contacts=56,
                 solver_iterations=50, **kw):
   """Solo8BaseConfig physics fields (gym_solo/core/configs.py:8-24) + the
   Bullet world defaults pybullet sets."""

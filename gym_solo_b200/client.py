@@ -318,6 +318,17 @@ class BatchedClient:
       pa = C.c_void_p(actions_ptr)     # the caller's own pinned buffer: no staging copy
     _lib.check(self.lib.solo_step_host(self.handle, pa, float(scale), po, pr, pd, self._stream()), self.handle)
 
+  def host_stepper(self, obs_ptr, reward_ptr, done_ptr):
+    """A closure over solo_step_host with everything but the action pointer and the scale bound:
+    the per-step host cost of Solo8VanillaEnv.step_host is one ctypes call."""
+    fn, handle, check, stream = self.lib.solo_step_host, self.handle, _lib.check, self._stream
+
+    def call(actions_ptr, scale):
+      rc = fn(handle, actions_ptr, scale, obs_ptr, reward_ptr, done_ptr, stream())
+      if rc:
+        check(rc, handle)
+    return call
+
   def set_link_friction(self, friction):
     """Per-env lateral friction of the non-base links ([N], None restores the model's
     value for every env): changeDynamics(lateralFriction=...) per environment."""

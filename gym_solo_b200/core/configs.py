@@ -46,7 +46,7 @@ class Solo8BaseConfig:
   control_mode: str = 'position'
   # Bullet world defaults the reference inherits from pybullet
   solver_iterations: int = 50
-  max_contacts: int = 64
+  max_contacts: int = 56
 
   @property
   def urdf(self):

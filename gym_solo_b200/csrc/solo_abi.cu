@@ -28,6 +28,7 @@ struct SoloHandle_ {
   int obs_dim;
   bool legpar;            // setup phase with one lane per (environment, leg): latency-bound batch sizes
   int block;              // threads per block of the one-thread-per-env kernels
+  bool solve_hiocc;       // solver instantiation held to 14 blocks per SM (throughput-bound batch sizes)
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
   bool bound;
@@ -97,6 +98,8 @@ static int pick_block(int n_envs) {
   if (n_envs <= 148 * 512) return 64;
   return 128;
 }
+
+constexpr int kHiOccEnvs = 10240;   // measured crossover between 8192 (-1.4 %) and 12288 (+1.3 %) environments
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -275,6 +278,10 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
 #endif
     if (h->legpar && h->block > 64) h->block = 64;   // 4 lanes per environment, 256-thread blocks
   }
+  // Up to a few waves of solver blocks the launch lasts as long as its slowest environment and the
+  // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
+  // and 14 instead of 12 resident warps per SM win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
+  h->solve_hiocc = n_envs >= kHiOccEnvs;
   h->motor_mask = 0;
   if (config->control_mode == SOLO_CONTROL_POSITION)
     for (int l = 0; l < model->n_legs; l++)
@@ -496,9 +503,11 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     SOLO_SETUP_LAUNCH(CH);                                                                                        \
     if ((rc = check_launch(h, "setup_kernel"))) return rc;                                                        \
     SOLO_MARK(1);                                                                                                 \
-    if (dbg) launch_ex(solve_warp_kernel<CH, true>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,     \
+    if (dbg) launch_ex(solve_warp_kernel<CH, true, 0>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,  \
                        n_cand, margin);                                                                           \
-    else launch_ex(solve_warp_kernel<CH, false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,       \
+    else if (h->solve_hiocc) launch_ex(solve_warp_kernel<CH, false, 14>, h->B.n, 32, 0, st, pdl, h->K.C, h->B,    \
+                                       h->motor_mask, ndof, n_cand, margin);                                      \
+    else launch_ex(solve_warp_kernel<CH, false, 0>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,    \
                    n_cand, margin);                                                                               \
     if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
     SOLO_MARK(2);                                                                                                 \
@@ -625,12 +634,17 @@ static int step_impl(SoloHandle h, const float *actions_dev, float action_scale,
     return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
   }
   static uint64_t tick = 0;
+  // One graph per output set (env.step hands out a ring of two; the host entry has one pinned
+  // block).  The action buffer changes from call to call -- fresh tensors, a pool of pinned host
+  // buffers -- and is patched into the setup nodes (2-3 us; capturing and instantiating a graph
+  // per buffer costs 1.4 ms each, measured).
+  constexpr size_t kMaxGraphs = 8;
   StepGraph *g = nullptr;
   for (StepGraph *c : h->graphs)
     if (c->obs == obs_dev && c->reward == reward_dev && c->done == done_dev && c->terminal == terminal_obs_dev &&
         c->scale == action_scale) { g = c; break; }
   if (!g) {
-    if (h->graphs.size() >= 8) {   // callers that allocate fresh outputs every step: evict the oldest
+    if (h->graphs.size() >= kMaxGraphs) {   // callers that allocate fresh outputs every step: evict the oldest
       size_t lru = 0;
       for (size_t i = 1; i < h->graphs.size(); i++) if (h->graphs[i]->used < h->graphs[lru]->used) lru = i;
       StepGraph *old = h->graphs[lru];
@@ -770,6 +784,10 @@ int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
       return SOLO_OK;
     case SOLO_OPT_ZERO_COPY:
       h->zero_copy = value != 0;
+      return SOLO_OK;
+    case SOLO_OPT_SOLVER_OCCUPANCY:
+      h->solve_hiocc = value < 0 ? h->B.n >= kHiOccEnvs : value != 0;
+      drop_graphs(h);
       return SOLO_OK;
     default:
       return fail(h, SOLO_EINVAL, "unknown option");

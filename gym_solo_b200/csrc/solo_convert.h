@@ -82,7 +82,7 @@ inline std::string convert_config(const SoloConfig &c, ConfigT<T> *out) {
   ConfigT<T> &o = *out;
   if (!(c.dt > 0)) return "dt must be positive";
   if (c.solver_iterations < 0) return "solver_iterations must be >= 0";
-  if (c.max_contacts < 0 || c.max_contacts > kMaxContacts) return "max_contacts out of range (0..64)";
+  if (c.max_contacts < 0 || c.max_contacts > kMaxContacts) return "max_contacts out of range (0..56)";
   if (c.control_mode != SOLO_CONTROL_POSITION && c.control_mode != SOLO_CONTROL_TORQUE) return "bad control_mode";
   o.dt = (T)c.dt; o.inv_dt = (T)(1.0 / c.dt);
   for (int i = 0; i < 3; i++) o.gravity[i] = (T)c.gravity[i];
@@ -95,6 +95,7 @@ inline std::string convert_config(const SoloConfig &c, ConfigT<T> *out) {
   o.lim_erp = (T)c.joint_limit_erp; o.lim_max = (T)c.joint_limit_max_impulse;
   o.iters = c.solver_iterations; o.substeps = c.num_substeps > 0 ? c.num_substeps : 1;
   o.control_mode = c.control_mode; o.max_contacts = c.max_contacts;
+
   return "";
 }
 

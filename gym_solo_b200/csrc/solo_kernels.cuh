@@ -217,11 +217,11 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
     float yb[6], yl[kLegs][CH];
     const float *y = B.yh + env;
 #pragma unroll
-    for (int a = 0; a < 6; a++) yb[a] = y[(int64_t)a * B.n];
+    for (int a = 0; a < 6; a++) yb[a] = __ldcg(y + (int64_t)a * B.n);
 #pragma unroll
     for (int l = 0; l < kLegs; l++)
 #pragma unroll
-      for (int k = 0; k < CH; k++) yl[l][k] = y[(int64_t)(6 + l * CH + k) * B.n];
+      for (int k = 0; k < CH; k++) yl[l][k] = __ldcg(y + (int64_t)(6 + l * CH + k) * B.n);
     finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
     // A non-finite state ends the episode: the environment restarts from its reset snapshot, the
     // step reports done = 1 (epilogue steps), the termination counters and the running episode
@@ -236,7 +236,7 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
   if (B.diag) {
     // fold this step's per-env solver statistics into the running totals
     const float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
-    diag_add(B.diag, live ? (int)st[(int64_t)B.n] : 0, live ? (int)st[0] : 0, nan, live ? 1 : 0);
+    diag_add(B.diag, live ? (int)__ldcg(st + (int64_t)B.n) : 0, live ? (int)__ldcg(st) : 0, nan, live ? 1 : 0);
   }
   if (!epilogue) {
     if (live) store_state<float, CH, float>(M, s, B.state + env, B.n);

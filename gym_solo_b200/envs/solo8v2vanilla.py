@@ -229,34 +229,41 @@ class Solo8VanillaEnv(Solo8BaseEnv):
     if plan is None:
       raise ValueError('step_host needs built-in observations, rewards and terminations')
     c = self.client
-    c.set_program(plan['program'], token=plan['token'])
-    if self._host is None or self._host['dim'] != plan['obs_dim']:
+    if c._program_token is not plan['token']:
+      c.set_program(plan['program'], token=plan['token'])
+    h = self._host
+    if h is None or h['token'] is not plan['token']:
       c.bind_staging(plan['obs_dim'])
-      # one pinned block laid out as the device staging (obs | reward | done): a single D2H
+      # one pinned block laid out as the device staging (obs | reward | done)
       d, n = plan['obs_dim'], c.n
       out = torch.empty((n * (d * 4 + 4 + 1),), dtype=torch.uint8).pin_memory()
-      self._host = dict(dim=d, out=out,
-                        act=torch.empty((n, c.n_api), dtype=torch.float32).pin_memory(),
-                        obs=out[:n * d * 4].view(torch.float32).view(n, d),
-                        rew=out[n * d * 4:n * d * 4 + n * 4].view(torch.float32),
-                        done=out[n * d * 4 + n * 4:])
+      h = self._host = dict(token=plan['token'], out=out,
+                            act=torch.empty((n, c.n_api), dtype=torch.float32).pin_memory(),
+                            obs=out[:n * d * 4].view(torch.float32).view(n, d),
+                            rew=out[n * d * 4:n * d * 4 + n * 4].view(torch.float32),
+                            done=out[n * d * 4 + n * 4:], pinned=set())
       # numpy views of the pinned block, made once (the returned arrays alias it: they are
       # overwritten by the next step_host, like the staging buffers of any vector env)
-      hh = self._host
-      hh['np'] = (hh['act'].numpy(), hh['obs'].numpy(), hh['rew'].numpy(), hh['done'].numpy())
-      hh['done_bool'] = hh['np'][3].view(np.bool_)
-      hh['info'] = {'labels': plan['labels']}
-    h = self._host
-    a, o, r, dn = h['np']
-    if (torch.is_tensor(action) and action.device.type == 'cpu' and action.dtype == torch.float32
-        and action.is_contiguous() and action.numel() == c.n * c.n_api and action.is_pinned()):
-      # actions already in page-locked host memory (torch.empty(...).pin_memory()): copied to the
-      # device straight from there
-      c.step_host(a, self._scale(), o, r, dn, actions_ptr=action.data_ptr())
-    else:
-      a[...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
-      c.step_host(a, self._scale(), o, r, dn)
-    return o, r, h['done_bool'], h['info']
+      h['np'] = (h['act'].numpy(), h['obs'].numpy(), h['rew'].numpy(), h['done'].numpy())
+      h['ret'] = (h['np'][1], h['np'][2], h['np'][3].view(np.bool_), {'labels': plan['labels']})
+      h['act_ptr'] = h['act'].data_ptr()
+      h['call'] = c.host_stepper(h['obs'].data_ptr(), h['rew'].data_ptr(), h['done'].data_ptr())
+    ptr = None
+    if type(action) is torch.Tensor:
+      p = action.data_ptr()
+      if p in h['pinned']:
+        ptr = p
+      elif (action.device.type == 'cpu' and action.dtype == torch.float32 and action.is_contiguous()
+            and action.numel() == c.n * c.n_api and action.is_pinned()):
+        # actions already in page-locked host memory (torch.empty(...).pin_memory()): read in place
+        # (the C side checks the pointer again on every call and stages it if it is not page-locked)
+        h['pinned'].add(p)
+        ptr = p
+    if ptr is None:
+      h['np'][0][...] = np.asarray(action, dtype=np.float32).reshape(c.n, c.n_api)
+      ptr = h['act_ptr']
+    h['call'](ptr, self._scale())
+    return h['ret']
 
   # ---- reset ----------------------------------------------------------------------
   def reset(self, init_call: bool = False, mask=None):

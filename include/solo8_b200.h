@@ -83,9 +83,11 @@ typedef struct SoloConfig {
   int32_t solver_iterations;      /* 50 */
   int32_t num_substeps;           /* physics steps of dt per action (reference: 1) */
   int32_t control_mode;           /* 0 = POSITION_CONTROL, 1 = torque */
-  int32_t max_contacts;           /* cap on simultaneous contact points per env */
+  int32_t max_contacts;           /* cap on simultaneous contact points per env, in Bullet's order
+                                     (by body, then by support point); <= SOLO_MAX_CONTACTS */
 } SoloConfig;
 
+#define SOLO_MAX_CONTACTS 56
 #define SOLO_CONTROL_POSITION 0
 #define SOLO_CONTROL_TORQUE 1
 
@@ -232,12 +234,16 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
                    float *obs_host, float *reward_host, uint8_t *done_host,
                    void *stream);
 
-/* Execution options (A/B measurements, debugging); both default to 1.
+/* Execution options (A/B measurements, debugging); the first two default to 1.
  *  SOLO_OPT_GRAPH      solo_step / solo_step_host replay one captured CUDA graph per
  *                      set of output buffers instead of 3 x num_substeps launches
- *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies */
+ *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies
+ *  SOLO_OPT_SOLVER_OCCUPANCY  which build of the solver kernel runs: 0 = 166 registers / 12
+ *                      blocks per SM (latency: small batches), 1 = 144 registers / 14 blocks per
+ *                      SM (throughput: large batches), -1 = by batch size (default) */
 #define SOLO_OPT_GRAPH 1
 #define SOLO_OPT_ZERO_COPY 2
+#define SOLO_OPT_SOLVER_OCCUPANCY 3
 int solo_set_option(SoloHandle h, int32_t option, int32_t value);
 
 /* Layout of the snapshot buffer bound with solo_bind: per_env = 0 (default) one

@@ -106,10 +106,10 @@ def test_render_other_cameras_sizes_and_shading():
       assert 1.0 - same.mean() <= MAX_BAD_FRACTION, (k['size'], i, 1.0 - same.mean())
       assert set(np.unique(seg[i])) <= {-1, 0, 1} and (seg[i] == 1).any()
       # where both agree on what was hit, the depth buffers agree: 1e-6 on average (float32 ndc
-      # depth has 6e-8 resolution near the far plane, the oracle is float64), 2e-4 at worst (sliver
+      # depth has 6e-8 resolution near the far plane, the oracle is float64), 3e-4 at worst (sliver
       # triangles: their affine depth equation has coefficients of order 1 / area)
       err = np.abs(depth[i] - want_depth)[same]
-      assert err.mean() <= 1e-6 and err.max() <= 2e-4, (err.mean(), err.max())
+      assert err.mean() <= 1e-6 and err.max() <= 3e-4, (err.mean(), err.max())
       assert (depth[i][seg[i] == -1] == 1.0).all() and depth[i].min() >= 0.0
     # the images that were not asked for are not produced
     _, _, _, d0, s0 = c.getCameraImage(w, h, view, proj, env_begin=0, env_count=1, depth=False, segmentation=False)

@@ -1,8 +1,10 @@
-"""A/B of solver builds on one box: for every library given (build/variants/lib_*.so, built with
--DSOLO_V_* switches) a fresh process runs the bench workload (configs[1]) at the sizes given and
-prints per-kernel times, the slowest environment's solver cycles and a checksum of the state.
+"""A/B of solver builds / execution options on one box: for every variant given a fresh process
+runs a bench workload at the sizes given and prints per-kernel times, the slowest environment's
+solver cycles and a checksum of the state.  A variant is a library (build/variants/lib_*.so built
+with -D switches; `product` = the in-tree library), optionally followed by @opt=value pairs for
+solo_set_option (graph, zero_copy, occ).
 
-  python tools/solver_ab.py 4096,65536 build/variants/lib_base.so build/variants/lib_fused.so ...
+  python tools/solver_ab.py 4096,65536 [cfg=2] product product@occ=1 build/variants/lib_x.so
 """
 import json, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -12,12 +14,16 @@ import json, os, sys
 import numpy as np, torch
 sys.path.insert(0, %(root)r)
 from gym_solo_b200 import _lib
-_lib.LIB_PATH = %(lib)r
+if %(lib)r:
+  _lib.LIB_PATH = %(lib)r
 import bench
+from gym_solo_b200 import _abi
 n = %(n)d
 cfg = %(cfg)d
 dev = torch.device('cuda', 0)
 env = bench.make_env(cfg, n, dev)
+for name, val in %(opts)r:
+  env.client.set_option({'graph': _abi.OPT_GRAPH, 'zero_copy': _abi.OPT_ZERO_COPY, 'occ': _abi.OPT_SOLVER_OCCUPANCY}[name], val)
 K = bench.CONFIGS[cfg]
 gen = torch.Generator(device=dev).manual_seed(1234)
 acts = [(torch.rand((n, K['n_api']), generator=gen, device=dev) * 2 - 1) * float(K['bound']) for _ in range(64)]
@@ -44,6 +50,19 @@ env.client.phase_timing(False)
 out['phase_ms'] = [round(m / cnt, 5) for m in pm]
 out['max_cycles_mean'] = float(np.mean(mx))
 out['checksum'] = float(env.get_state().double().abs().sum())
+# end to end: synchronous step_host from a pool of pinned action buffers
+import time
+host = [torch.from_numpy(np.random.RandomState(k).uniform(-1, 1, (n, K['n_api'])).astype(np.float32) * float(K['bound'])).pin_memory() for k in range(16)]
+for k in range(20): env.step_host(host[k %% 16])
+t0 = time.perf_counter()
+for k in range(reps): o, r, d, _ = env.step_host(host[k %% 16]); x = float(r[0])
+out['e2e_us'] = 1e6 * (time.perf_counter() - t0) / reps
+for k in range(reps): env.step(acts[k %% 64])
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for k in range(reps): env.step(acts[k %% 64])
+torch.cuda.synchronize()
+out['b2b_us'] = 1e6 * (time.perf_counter() - t0) / reps
 print(json.dumps(out))
 '''
 
@@ -54,11 +73,13 @@ def main():
   if libs and libs[0].startswith('cfg='):
     cfg = int(libs[0][4:]); libs = libs[1:]
   for n in sizes:
-    for lib in libs:
-      code = CHILD % dict(root=ROOT, lib=os.path.abspath(lib), n=n, cfg=cfg)
+    for spec in libs:
+      lib, *rest = spec.split('@')
+      opts = [(x.split('=')[0], int(x.split('=')[1])) for x in rest]
+      code = CHILD % dict(root=ROOT, lib='' if lib == 'product' else os.path.abspath(lib), n=n, cfg=cfg, opts=opts)
       r = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True)
       line = r.stdout.strip().splitlines()[-1] if r.stdout.strip() else 'FAILED: ' + r.stderr[-400:]
-      print(n, os.path.basename(lib), line, flush=True)
+      print(n, spec, line, flush=True)
 
 if __name__ == '__main__':
   main()
