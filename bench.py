@@ -107,30 +107,26 @@ def hbm_peak():
   return 6650.0, 'fallback'
 
 
-def ncu_instructions(kernel, n_envs):
-  """smsp__inst_executed.sum of one launch of `kernel` from the same capture, or None."""
+def _capture(n_envs):
+  """profiles/traffic.json: numbers of the committed `ncu --set full` captures, per batch size."""
   p = os.path.join(ROOT, 'profiles', 'traffic.json')
   try:
-    t = json.load(open(p))
-    if int(t.get('envs', -1)) == int(n_envs):
-      return t['warp_instructions_per_launch'].get(kernel)
+    return json.load(open(p)).get('by_envs', {}).get(str(int(n_envs)))
   except Exception:
-    pass
-  return None
+    return None
+
+
+def ncu_instructions(kernel, n_envs):
+  """smsp__inst_executed.sum of one launch of `kernel` from the capture at this batch size, or None."""
+  c = _capture(n_envs)
+  return c['warp_instructions_per_launch'].get(kernel) if c else None
 
 
 def ncu_traffic(kernel, n_envs):
-  """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the
-  committed `ncu --set full` capture (profiles/traffic.json, taken at 4096 envs with
-  ncu's cold caches); None for any other batch size."""
-  p = os.path.join(ROOT, 'profiles', 'traffic.json')
-  try:
-    t = json.load(open(p))
-    if int(t.get('envs', -1)) == int(n_envs):
-      return t['dram_bytes_per_launch'].get(kernel)
-  except Exception:
-    pass
-  return None
+  """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed
+  `ncu --set full` capture at this batch size (ncu's cold caches); None without one."""
+  c = _capture(n_envs)
+  return c['dram_bytes_per_launch'].get(kernel) if c else None
 
 
 def issue_util(kernel, n_envs, launch_ms, clocks):

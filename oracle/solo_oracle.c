@@ -9,8 +9,12 @@
  *   (gym_solo/envs/solo8v2vanilla.py:87-91)
  * lives in the third-party `pybullet` wheel (unpinned, setup.py:7), which is
  * neither under /root/reference nor installable here or on the GPU box
- * (gpurun_out/probe.txt).  The reference's own tests pin no post-step numbers
- * (SURVEY.md section 8c).  This file restates Bullet's published
+ * (profiles/r2_box_probe.txt).  The reference's own tests pin no post-step numbers
+ * (SURVEY.md section 8c).  What the reference does hold pins this file on the CPU
+ * (tests/test_joint_info_golden.py: the 12 golden getJointInfo tuples for the model;
+ * tests/test_oracle_reference_properties.py: the examples' standing height 0.33698, the
+ * rest-state / response / reset properties of gym_solo/envs/test_solo8v2vanilla.py).
+ * This file restates Bullet's published
  * btMultiBodyDynamicsWorld step from recollection:
  *   B2 step order: contacts at current pose -> forces + ABA -> v += a dt ->
  *      rows -> PGS -> v += dv -> integrate (semi-implicit, exponential map)

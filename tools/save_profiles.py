@@ -3,12 +3,15 @@ round tag: bench lines, the ncu launch list, key rows of the `ncu --set full`
 captures (one csv per kernel), per-source-line stall tables, and
 profiles/traffic.json (dram bytes per launch, read by bench.py's roofline.traffic).
 
-  python tools/save_profiles.py r1f setup_legpar_kernel solve_warp_kernel finish_kernel
+  python tools/save_profiles.py r1f [--envs=N] setup_legpar_kernel solve_warp_kernel finish_kernel
 """
 import csv, io, json, os, shutil, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OUT, PROF = os.path.join(ROOT, 'gpurun_out'), os.path.join(ROOT, 'profiles')
 tag, kernels = sys.argv[1], sys.argv[2:]
+envs = 4096
+if kernels and kernels[0].startswith('--envs='):
+  envs = int(kernels[0].split('=')[1]); kernels = kernels[1:]
 WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum', 'lts__t_bytes.sum',
         'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__thread_inst_executed_per_inst_executed.ratio',
         'sm__warps_active.avg.pct_of_peak_sustained_active', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
@@ -42,11 +45,23 @@ for k in kernels:
     return float(v.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
   traffic[k] = byt('dram__bytes_read.sum') + byt('dram__bytes_write.sum')
   insts[k] = float(d['smsp__inst_executed.sum'][1].replace(',', ''))
-  sub = {'setup_kernel': 'setup_kernel+ILi2E', 'setup_legpar_kernel': 'setup_legpar_kernel+ILi2E', 'solve_warp_kernel': 'solve_warp_kernel+ILi2ELb0', 'finish_kernel': 'finish_kernel+ILi2E',
+  sub = {'setup_kernel': 'setup_kernel+ILi2E', 'setup_legpar_kernel': 'setup_legpar_kernel+ILi2E', 'solve_warp_kernel': 'solve_warp_kernel+ILi2ELb0ELi14' if envs >= 10240 else 'solve_warp_kernel+ILi2ELb0ELi0', 'finish_kernel': 'finish_kernel+ILi2E',
          'solve_gram_kernel': 'solve_gram_kernel+ILi2ELb0'}.get(k, k)
   txt = subprocess.run([sys.executable, os.path.join(ROOT, 'tools', 'ncu_lines.py'), rep, sub, '40'], text=True,
                        capture_output=True).stdout
   open(os.path.join(PROF, '%s_%s_lines.txt' % (tag, k)), 'w').write(txt)
-json.dump({'envs': 4096, 'round': tag, 'how': 'ncu --set full --clock-control none, one launch inside bench.py (cold caches: ncu flushes between passes)',
-           'dram_bytes_per_launch': traffic, 'warp_instructions_per_launch': insts}, open(os.path.join(PROF, 'traffic.json'), 'w'), indent=1)
-print(traffic)
+path = os.path.join(PROF, 'traffic.json')
+try:
+  allt = json.load(open(path))
+except Exception:
+  allt = {}
+by = allt.get('by_envs', {})
+cur = by.get(str(envs), {'dram_bytes_per_launch': {}, 'warp_instructions_per_launch': {}})
+cur['round'] = tag
+cur['dram_bytes_per_launch'].update(traffic)
+cur['warp_instructions_per_launch'].update(insts)
+by[str(envs)] = cur
+allt = {'how': 'ncu --set full --clock-control none, one launch inside bench.py (cold caches: ncu flushes between passes); '
+               'per batch size (environments per GPU)', 'by_envs': by}
+json.dump(allt, open(path, 'w'), indent=1)
+print(envs, traffic)

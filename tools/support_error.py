@@ -2,9 +2,10 @@
 STL convex hull?  For a plane the contact point of a convex hull is its support point in the
 direction of the plane normal, so the error of the reduction in a direction d is
   h_full(d) - h_reduced(d) >= 0   (metres; the reduced set is a subset of the hull),
-i.e. how far the real hull would reach below the lowest retained point.  Reported per link as the
-maximum and the 99th percentile over 10^4 uniformly random directions, and over the directions
-within 30 degrees of the link's -z (the underside the folded reset pose rests on).
+i.e. how far the real hull would reach below the lowest retained point.  Reported per BODY (a link plus
+the links fixed to it) as the maximum, the 99th percentile and the mean over 10^4 uniformly random
+directions, and the maximum over the directions within 30 degrees of the body's -z (the underside
+the folded reset pose rests on).
 
 Needs the reference's meshes (/root/reference): authoring container only.
   python tools/support_error.py [blob.json]
@@ -27,23 +28,28 @@ def main():
   from scipy.spatial import ConvexHull
   cand_pos = np.array(blob['cand_pos']); cand_link = np.array(blob['cand_link'])
   out = {}
-  parts = {L['name']: L for L in blob['links']}
-  for name, L in links.items():
-    if L['mesh'] is None or not os.path.exists(os.path.join(mesh_dir, L['mesh'])):
+  for b, body in enumerate(blob['body_names']):
+    clouds = []
+    for P in blob['links']:
+      if P['body'] != b:
+        continue
+      L = links[P['name']]
+      if L['mesh'] is None or not os.path.exists(os.path.join(mesh_dir, L['mesh'])):
+        continue
+      v = cm.read_stl(os.path.join(mesh_dir, L['mesh']))
+      hv = v[ConvexHull(v).vertices]
+      p, R = np.array(P['pos']), np.array(P['rot'])
+      clouds.append(p + (R @ (L['cxyz'][:, None] + L['cR'] @ hv.T)).T)      # BODY coordinates, like the candidates
+    if not clouds:
       continue
-    v = cm.read_stl(os.path.join(mesh_dir, L['mesh']))
-    hv = v[ConvexHull(v).vertices]
-    # full hull in BODY coordinates, like the candidates
-    P = parts[name]
-    p, R = np.array(P['pos']), np.array(P['rot'])
-    full = (p + (R @ (L['cxyz'][:, None] + L['cR'] @ hv.T)).T)
-    red = cand_pos[cand_link == name]
+    full = np.concatenate(clouds)
+    red = cand_pos[np.array(blob['cand_body']) == b]
     e = (full @ dirs.T).max(0) - (red @ dirs.T).max(0)
-    down = -R[:, 2]                      # the link's own -z in body coordinates
-    under = dirs @ down > np.cos(np.radians(30))
-    out[name] = dict(hull_vertices=int(len(hv)), points=int(len(red)), max_mm=float(1e3 * e.max()),
+    under = dirs[:, 2] < -np.cos(np.radians(30))          # within 30 degrees of the body's -z
+    out[body] = dict(hull_points=int(len(full)), points=int(len(red)), max_mm=float(1e3 * e.max()),
                      p99_mm=float(1e3 * np.percentile(e, 99)), mean_mm=float(1e3 * e.mean()),
-                     underside_max_mm=float(1e3 * e[under].max()))
+                     underside_max_mm=float(1e3 * e[under].max()),
+                     recorded_by_compiler_mm=1e3 * blob.get('support_error', {}).get(body, float('nan')))
   print(json.dumps(out, indent=1))
 
 
