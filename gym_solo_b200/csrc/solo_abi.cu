@@ -126,6 +126,13 @@ static size_t tile_smem(const SoloHandle h) {
   return (size_t)h->block * (size_t)(k | 1) * sizeof(float);
 }
 
+// setup_legpar_kernel: the action tile + the block's KinLayout records (bulk-stored at the end)
+static size_t setup_smem(const SoloHandle h) {
+  const size_t tile = (((size_t)h->block * (size_t)(h->K.M.n_api | 1) + 3) & ~(size_t)3) * sizeof(float);
+  const size_t rec = (size_t)h->block * (h->ch == 2 ? KinLayout<2>::kSize : KinLayout<3>::kSize) * sizeof(float);
+  return tile + rec;
+}
+
 template <typename F>
 static int opt_in_smem(SoloHandle h, F *kernel, size_t bytes) {
   if (bytes <= 48 * 1024) return SOLO_OK;
@@ -314,6 +321,10 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
       delete h;
       return fail(nullptr, SOLO_ENOGPU, "device is not sm_100 class: this library is built for sm_100a only");
     }
+    // the setup kernel's shared memory (records of a block) is above 48 KB for 3-joint chains
+    int rc = h->ch == 2 ? opt_in_smem(h, setup_legpar_kernel<2>, setup_smem(h))
+                        : opt_in_smem(h, setup_legpar_kernel<3>, setup_smem(h));
+    if (rc) { std::string m = h->err; delete h; return fail(nullptr, rc, m); }
   }
   *out = h;
   return SOLO_OK;
@@ -348,14 +359,14 @@ int solo_set_program(SoloHandle h, const SoloProgram *program) {
 #ifdef SOLO_EXPERIMENTS
     if (!rc) rc = opt_in_smem(h, setup_kernel<2>, sm);
 #endif
-    if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<2>, sm);
+    if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<2>, setup_smem(h));
     if (!rc) rc = opt_in_smem(h, finish_kernel<2>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<2>, sm);
   } else {
 #ifdef SOLO_EXPERIMENTS
     if (!rc) rc = opt_in_smem(h, setup_kernel<3>, sm);
 #endif
-    if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<3>, sm);
+    if (!rc) rc = opt_in_smem(h, setup_legpar_kernel<3>, setup_smem(h));
     if (!rc) rc = opt_in_smem(h, finish_kernel<3>, sm);
     if (!rc) rc = opt_in_smem(h, observe_kernel<3>, sm);
   }
@@ -519,13 +530,13 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
 #define SOLO_SETUP_LAUNCH(CH)                                                                                     \
   do {                                                                                                            \
     if (!h->legpar) setup_kernel<CH><<<grid, h->block, sm, st>>>(h->K, h->B, actions_dev, broadcast, action_scale); \
-    else launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, sm, st, false, h->K, h->B, actions_dev,           \
-                   broadcast, action_scale);                                                                      \
+    else launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, setup_smem(h), st, false, h->K, h->B,             \
+                   actions_dev, broadcast, action_scale);                                                                      \
   } while (0)
 #else
 #define SOLO_SETUP_LAUNCH(CH)                                                                                     \
-  launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, sm, st, false, h->K, h->B, actions_dev, broadcast,       \
-            action_scale)
+  launch_ex(setup_legpar_kernel<CH>, grid, 4 * h->block, setup_smem(h), st, false, h->K, h->B, actions_dev,       \
+            broadcast, action_scale)
 #endif
   if (h->ch == 2) SOLO_PHYSICS(2);
   else SOLO_PHYSICS(3);

@@ -308,7 +308,13 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
   }
   lim_bits |= __shfl_xor_sync(0xffffffffu, lim_bits, 1);
   lim_bits |= __shfl_xor_sync(0xffffffffu, lim_bits, 2);
-  if (!live) return;
+
+  // The records of the block's environments are contiguous in memory ([env][KinLayout::kSize]):
+  // they are assembled in shared memory and leave as ONE bulk copy (cp.async.bulk, the 1-D form of
+  // TMA) issued by one thread, instead of 328 scattered 4-byte stores per environment whose queue
+  // (lg_throttle) the four lanes would wait on.
+  float *rec = smem + ((epb * pad_stride(n_api) + 3) & ~3);
+  if (live) {
 
   // ---- factors for finish_step (FactorLayout) ----
   {
@@ -339,7 +345,7 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
   // ---- motor rows of the own leg (POSITION_CONTROL) and joint-limit rows ----
   // a joint at or beyond a URDF limit gets Bullet's unilateral limit row; it shares the motor
   // row's whitened direction (J = +-e_j), so the slot is built whenever either row is live
-  float *kin = B.kin + env * KL::kSize;
+  float *kin = rec + slot * KL::kSize;
   const bool motors = (C.control_mode == 0);
 #pragma unroll
   for (int i = 0; i < CH; i++) {
@@ -396,6 +402,8 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
 #pragma unroll
     for (int i = 0; i < 9; i++) kin[KL::kR0 + i] = R0.m[i];
     kin[KL::kLim] = __uint_as_float(lim_bits);
+#pragma unroll
+    for (int i = KL::kLim + 1; i < KL::kSize; i++) kin[i] = 0.f;   // padding of the record
   }
   {
     float *kl = kin + KL::kLeg + l * KL::kLegSize;
@@ -418,6 +426,17 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
 #pragma unroll
       for (int i = 0; i < 9; i++) kj[6 + i] = jR[j].m[i];
     }
+  }
+  }   // live
+  __syncthreads();
+  if (threadIdx.x == 0 && n_valid > 0) {
+    const uint32_t src = (uint32_t)__cvta_generic_to_shared(rec);
+    float *dst = B.kin + env0 * KL::kSize;
+    const uint32_t bytes = (uint32_t)n_valid * KL::kSize * sizeof(float);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the generic-proxy writes above, before the async copy reads them
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // complete (and visible) before the block exits
   }
 }
 

@@ -31,6 +31,22 @@
 #include "solo_contact.cuh"
 #include "solo_kernels.cuh"
 
+// -DSOLO_CHECKS (tools/sanitizer_run.py; compute-sanitizer is closed on this pool): every index into
+// the warp's shared arrays and the candidate table is checked; a violation prints and traps.
+#ifdef SOLO_CHECKS
+#include <stdio.h>
+#define SOLO_CHECK(cond)                                                                     \
+  do {                                                                                       \
+    if (!(cond)) {                                                                           \
+      printf("SOLO_CHECK failed: %s (%s:%d) block %d lane %d\n", #cond, __FILE__, __LINE__, \
+             (int)blockIdx.x, (int)threadIdx.x);                                             \
+      __trap();                                                                              \
+    }                                                                                        \
+  } while (0)
+#else
+#define SOLO_CHECK(cond) do { } while (0)
+#endif
+
 namespace solo {
 
 // one active contact in shared memory (floats)
@@ -152,6 +168,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
     const int c = lane + 32 * r;
     const bool valid = c < nc;
     const int cand = valid ? sm.list[c] : 0;
+    SOLO_CHECK(cand >= 0 && cand < kMaxCand && nc <= kMaxContacts && nc <= 32 * NR);
     const Cand k = load_cand(cand_tab, cand);
     float row[1][RL::kRow];
     build_contact_rows<CH, 1>(sm.kin, C, margin, k, cand, row);
@@ -300,6 +317,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
           if (viol != 0) {
             // ---- promotion of contact v into slot k (rare) ----
             const int v = MK::first(viol);
+            SOLO_CHECK(v >= 0 && v < nc && ((act >> v) & 1) == 0 && n_act < nc && n_act < kMaxContacts && k <= n_act);
             float dv = __shfl_sync(FULL, t[0], v & 31);
             if (NR > 1) {
               const float d1 = __shfl_sync(FULL, t[NR - 1], v & 31);
@@ -336,6 +354,8 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
           }
         }
         if (at_end) break;
+        SOLO_CHECK(k >= 0 && k < n_act && __float_as_int(m0.w) >= 0 && __float_as_int(m0.w) < nc &&
+                   ((act >> __float_as_int(m0.w)) & 1) == 1 && (k == 0 || __float_as_int(sm.ent[k - 1][AL::kMeta + 3]) < __float_as_int(m0.w)));
         const float lam_n = m0.x;
         const float sum = fmaxf(dense_gap<W>(nr, y, lam_n), 0.f);
         const float d = sum - lam_n;
@@ -440,6 +460,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
 #pragma unroll
     for (int i = 0; i < kRounds; i++) {
       const int rank = before + __popc(hits[i] & ((1u << lane) - 1u));
+      SOLO_CHECK(C.max_contacts <= kMaxContacts);
       if (((hits[i] >> lane) & 1u) && rank < C.max_contacts) sm.list[rank] = lane + 32 * i;
       before += __popc(hits[i]);
     }

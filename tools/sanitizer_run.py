@@ -1,4 +1,7 @@
-"""Workload for compute-sanitizer (memcheck / racecheck / synccheck): 64 environments, reset (the
+"""Workload for a -DSOLO_CHECKS build of the library (every index into the solver warp's shared
+arrays checked; compute-sanitizer itself is closed on this pool, profiles/r2_compute_sanitizer_closed.txt):
+  python tools/sanitizer_run.py build/variants/lib_checks.so
+64 environments, reset (the
 500 settle steps), 50 env.steps with random actions, then a belly-flop state with more than 32
 contacts so that the two-rows-per-lane instantiation warp_solve<CH, 2> and its promotions run,
 the torque / limit-row path, and one render call.
@@ -10,6 +13,9 @@ import numpy as np
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+if len(sys.argv) > 1:
+  from gym_solo_b200 import _lib
+  _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 import bench
 
 dev = torch.device('cuda', 0)
