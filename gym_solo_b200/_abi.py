@@ -38,6 +38,7 @@ REW_MUL = 17
 OPT_GRAPH = 1
 OPT_ZERO_COPY = 2
 OPT_SOLVER_OCCUPANCY = 3
+OPT_FINISH_WARMUP = 4
 
 TERM_PERPETUAL = 1
 TERM_TIME = 2

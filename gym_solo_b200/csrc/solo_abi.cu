@@ -29,6 +29,7 @@ struct SoloHandle_ {
   bool legpar;            // setup phase with one lane per (environment, leg): latency-bound batch sizes
   int block;              // threads per block of the one-thread-per-env kernels
   bool solve_hiocc;       // solver instantiation held to 14 blocks per SM (throughput-bound batch sizes)
+  bool warm_finish;       // finish_kernel runs a dry pass behind the solver (small batches: fetch bound)
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
   bool bound;
@@ -290,6 +291,7 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
   // and 14 instead of 12 resident warps per SM win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
   h->solve_hiocc = n_envs >= kHiOccEnvs;
+  h->warm_finish = n_envs < kHiOccEnvs;
   h->motor_mask = 0;
   if (config->control_mode == SOLO_CONTROL_POSITION)
     for (int l = 0; l < model->n_legs; l++)
@@ -523,8 +525,8 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
                    n_cand, margin);                                                                               \
     if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
     SOLO_MARK(2);                                                                                                 \
-    launch_ex(finish_kernel<CH>, grid, h->block, sm, st, pdl, h->K, h->B, epilogue, obs_dev, reward_dev,          \
-              done_dev, terminal_obs_dev);                                                                        \
+    launch_ex(finish_kernel<CH>, grid, h->block, sm, st, pdl, h->K, h->B, epilogue, (int)(pdl && h->warm_finish), \
+              obs_dev, reward_dev, done_dev, terminal_obs_dev);                                                   \
   } while (0)
 #ifdef SOLO_EXPERIMENTS
 #define SOLO_SETUP_LAUNCH(CH)                                                                                     \
@@ -796,6 +798,10 @@ int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
       return SOLO_OK;
     case SOLO_OPT_ZERO_COPY:
       h->zero_copy = value != 0;
+      return SOLO_OK;
+    case SOLO_OPT_FINISH_WARMUP:
+      h->warm_finish = value < 0 ? h->B.n < kHiOccEnvs : value != 0;
+      drop_graphs(h);
       return SOLO_OK;
     case SOLO_OPT_SOLVER_OCCUPANCY:
       h->solve_hiocc = value < 0 ? h->B.n >= kHiOccEnvs : value != 0;

@@ -425,12 +425,13 @@ SOLO_HD T compute_reward(const ModelT<T> &M, const ProgramC &P, const EnvState<T
 // TerminationFactory.is_terminated (termination.py:38-50): OR with short
 // circuit -- once a term fires, later TimeBasedTermination counters are not
 // ticked.  counters: int32 [term][stride].
-SOLO_HD bool eval_terminations(const ProgramC &P, int32_t *counters, int64_t stride) {
+// commit = false evaluates without ticking (finish_kernel's warm-up pass).
+SOLO_HD bool eval_terminations(const ProgramC &P, int32_t *counters, int64_t stride, const bool commit = true) {
   for (int t = 0; t < P.n_term; t++) {
     const TermTermC &tt = P.term[t];
     if (tt.kind == kTermTime) {   // termination.py:72-83
       const int32_t c = counters[t * stride] + 1;
-      counters[t * stride] = c;
+      if (commit) counters[t * stride] = c;
       if (c > tt.max_step_delta) return true;
     }
     // PerpetualTermination (termination.py:86-98): never fires

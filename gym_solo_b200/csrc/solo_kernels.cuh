@@ -138,7 +138,7 @@ __device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t
   __syncthreads();
 }
 __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0, int n_valid, int k,
-                                             const float *sm) {
+                                             const float *sm, const bool commit = true) {
   const int ps = pad_stride(k);
   const int total = n_valid * k;
   float *dst = g + env0 * k;
@@ -146,7 +146,8 @@ __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0
   __syncthreads();
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int r = tile_row(i, inv_k), c = i - r * k;
-    dst[i] = sm[r * ps + c];
+    const float v = sm[r * ps + c];
+    if (commit) dst[i] = v;
   }
 }
 
@@ -192,10 +193,17 @@ setup_kernel(const __grid_constant__ KParams K, const Buffers B, const float *__
 // env.step (solo8v2vanilla.py:96-102): observations, reward, termination,
 // optional in-kernel auto reset.
 // ---------------------------------------------------------------------------------
+// warm != 0 (the kernel was launched as a programmatic dependent of the solver): the whole body
+// runs once BEFORE cudaGridDependencySynchronize() with every side effect switched off, on
+// whatever yh holds at that moment.  At small batches one warp per SM walks ~6.6 k instructions
+// exactly once and the kernel was bound by instruction fetch (no_instruction + long_scoreboard);
+// the dry pass pulls the code and the factor lines in while the solver drains, and the pass that
+// counts finds them warm.
 template <int CH>
 __global__ void __launch_bounds__(128)
-finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epilogue, float *__restrict__ obs_out,
-              float *__restrict__ reward_out, uint8_t *__restrict__ done_out, float *__restrict__ terminal_obs_out) {
+finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epilogue, const int warm,
+              float *__restrict__ obs_out, float *__restrict__ reward_out, uint8_t *__restrict__ done_out,
+              float *__restrict__ terminal_obs_out) {
   extern __shared__ float smem[];
   const ModelT<float> &M = K.M;
   const ProgramC &P = K.P;
@@ -203,97 +211,109 @@ finish_kernel(const __grid_constant__ KParams K, const Buffers B, const int epil
   const int64_t env = env0 + threadIdx.x;
   const int n_valid = (int)min((int64_t)blockDim.x, (int64_t)B.n - env0);
   const bool live = env < B.n;
-
-  EnvState<float, CH> s;
-  float ob[kMaxObsDim];
-  float rew = 0.f;
-  bool done = false;
-  int nan = 0;
-  // programmatic dependent of solve_warp_kernel: the state (last written by the previous step's
-  // finish, which completed before this step's setup started) is fetched while the solver drains
-  if (live) load_state<float, CH, float>(M, B.state + env, B.n, s);
-  cudaGridDependencySynchronize();
-  if (live) {
-    float yb[6], yl[kLegs][CH];
-    const float *y = B.yh + env;
-#pragma unroll
-    for (int a = 0; a < 6; a++) yb[a] = __ldcg(y + (int64_t)a * B.n);
-#pragma unroll
-    for (int l = 0; l < kLegs; l++)
-#pragma unroll
-      for (int k = 0; k < CH; k++) yl[l][k] = __ldcg(y + (int64_t)(6 + l * CH + k) * B.n);
-    finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
-    // A non-finite state ends the episode: the environment restarts from its reset snapshot, the
-    // step reports done = 1 (epilogue steps), the termination counters and the running episode
-    // statistics start over, and diag[2] counts it (pybullet would hand the NaN to the caller).
-    if (!env_finite<CH>(s)) {
-      load_snapshot<CH>(M, B, env, s);
-      nan = 1;
-      for (int t = 0; t < kMaxTermTerms; t++) B.counters[(int64_t)t * B.n + env] = 0;
-      if (B.stats && !epilogue) { B.stats[env] = 0.f; B.stats[(int64_t)B.n + env] = 0.f; }
-    }
-  }
-  if (B.diag) {
-    // fold this step's per-env solver statistics into the running totals
-    const float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
-    diag_add(B.diag, live ? (int)__ldcg(st + (int64_t)B.n) : 0, live ? (int)__ldcg(st) : 0, nan, live ? 1 : 0);
-  }
-  if (!epilogue) {
-    if (live) store_state<float, CH, float>(M, s, B.state + env, B.n);
-    return;
-  }
-
-  if (live) {
-    float e[3];
-    euler_from_quat(s.quat, e);
-    compute_obs<float, CH>(M, P, s, e, ob);
-    rew = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
-    done = eval_terminations(P, B.counters + env, B.n);
-    if (nan) {
-      done = true;   // restarted from the snapshot above: the new episode has not ticked yet
-      for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
-    }
-    if (B.stats) {
-      float ret = B.stats[env] + rew;
-      float len = B.stats[(int64_t)B.n + env] + 1.f;
-      if (done) {
-        // totals over FINISHED episodes (episode_statistics: mean return / mean length)
-        B.stats[2 * (int64_t)B.n + env] += ret;
-        B.stats[3 * (int64_t)B.n + env] += 1.f;
-        B.stats[4 * (int64_t)B.n + env] += len;
-        if (P.auto_reset || nan) { ret = 0.f; len = 0.f; }
-      }
-      B.stats[env] = ret;
-      B.stats[(int64_t)B.n + env] = len;
-    }
-  }
-
   const int od = B.obs_dim;
   const int ps = pad_stride(od);
-  if (P.auto_reset) {
-    // terminal observation first (gym.vector convention), then the first
-    // observation of the new episode from the snapshot
-    if (terminal_obs_out) {
-      if (live)
-        for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
-      tile_scatter(terminal_obs_out, env0, n_valid, od, smem);
-      __syncthreads();
+
+#pragma unroll 1
+  for (int pass = warm ? 0 : 1; pass < 2; pass++) {
+    const bool commit = pass == 1;
+    // programmatic dependent of solve_warp_kernel: nothing the solver writes is trusted before this
+    if (commit) cudaGridDependencySynchronize();
+    EnvState<float, CH> s;
+    float ob[kMaxObsDim];
+    float rew = 0.f;
+    bool done = false;
+    int nan = 0;
+    if (live) {
+      load_state<float, CH, float>(M, B.state + env, B.n, s);
+      float yb[6], yl[kLegs][CH];
+      const float *y = B.yh + env;
+#pragma unroll
+      for (int a = 0; a < 6; a++) yb[a] = __ldcg(y + (int64_t)a * B.n);
+#pragma unroll
+      for (int l = 0; l < kLegs; l++)
+#pragma unroll
+        for (int k = 0; k < CH; k++) yl[l][k] = __ldcg(y + (int64_t)(6 + l * CH + k) * B.n);
+      finish_step<float, CH>(M, K.C, s, B.fac + env, B.n, yb, yl);
+      // A non-finite state ends the episode: the environment restarts from its reset snapshot, the
+      // step reports done = 1 (epilogue steps), the termination counters and the running episode
+      // statistics start over, and diag[2] counts it (pybullet would hand the NaN to the caller).
+      if (!env_finite<CH>(s)) {
+        load_snapshot<CH>(M, B, env, s);
+        nan = 1;
+        if (commit) {
+          for (int t = 0; t < kMaxTermTerms; t++) B.counters[(int64_t)t * B.n + env] = 0;
+          if (B.stats && !epilogue) { B.stats[env] = 0.f; B.stats[(int64_t)B.n + env] = 0.f; }
+        }
+      }
     }
-    if (live && done) {
-      load_snapshot<CH>(M, B, env, s);
-      for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
+    if (B.diag && commit) {
+      // fold this step's per-env solver statistics into the running totals
+      const float *st = B.yh + (int64_t)(6 + kLegs * CH) * B.n + env;
+      diag_add(B.diag, live ? (int)__ldcg(st + (int64_t)B.n) : 0, live ? (int)__ldcg(st) : 0, nan, live ? 1 : 0);
+    }
+    if (!epilogue) {
+      if (live && commit) store_state<float, CH, float>(M, s, B.state + env, B.n);
+      continue;
+    }
+
+    if (live) {
       float e[3];
       euler_from_quat(s.quat, e);
       compute_obs<float, CH>(M, P, s, e, ob);
+      rew = P.n_rew > 0 ? compute_reward<float, CH>(M, P, s, e) : 0.f;
+      done = eval_terminations(P, B.counters + env, B.n, commit);
+      if (nan) {
+        done = true;   // restarted from the snapshot above: the new episode has not ticked yet
+        if (commit)
+          for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
+      }
+      if (B.stats) {
+        float ret = B.stats[env] + rew;
+        float len = B.stats[(int64_t)B.n + env] + 1.f;
+        if (commit) {
+          if (done) {
+            // totals over FINISHED episodes (episode_statistics: mean return / mean length)
+            B.stats[2 * (int64_t)B.n + env] += ret;
+            B.stats[3 * (int64_t)B.n + env] += 1.f;
+            B.stats[4 * (int64_t)B.n + env] += len;
+            if (P.auto_reset || nan) { ret = 0.f; len = 0.f; }
+          }
+          B.stats[env] = ret;
+          B.stats[(int64_t)B.n + env] = len;
+        }
+      }
     }
+
+    if (P.auto_reset) {
+      // terminal observation first (gym.vector convention), then the first
+      // observation of the new episode from the snapshot
+      if (terminal_obs_out) {
+        if (live)
+          for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
+        tile_scatter(terminal_obs_out, env0, n_valid, od, smem, commit);
+        __syncthreads();
+      }
+      if (live && done) {
+        load_snapshot<CH>(M, B, env, s);
+        if (commit)
+          for (int t = 0; t < P.n_term; t++) B.counters[(int64_t)t * B.n + env] = 0;
+        float e[3];
+        euler_from_quat(s.quat, e);
+        compute_obs<float, CH>(M, P, s, e, ob);
+      }
+    }
+    if (live) {
+      if (commit) {
+        store_state<float, CH, float>(M, s, B.state + env, B.n);
+        reward_out[env] = rew;
+        done_out[env] = done ? 1 : 0;
+      }
+      for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
+    }
+    tile_scatter(obs_out, env0, n_valid, od, smem, commit);
+    __syncthreads();   // the tile is reused by the next pass
   }
-  if (live) {
-    store_state<float, CH, float>(M, s, B.state + env, B.n);
-    reward_out[env] = rew;
-    done_out[env] = done ? 1 : 0;
-    for (int i = 0; i < od; i++) smem[threadIdx.x * ps + i] = ob[i];
-  }
-  tile_scatter(obs_out, env0, n_valid, od, smem);
 }
 
 // obs_factory.get_obs() / reward_factory.get_reward() on the current state

@@ -240,10 +240,15 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies
  *  SOLO_OPT_SOLVER_OCCUPANCY  which build of the solver kernel runs: 0 = 166 registers / 12
  *                      blocks per SM (latency: small batches), 1 = 144 registers / 14 blocks per
- *                      SM (throughput: large batches), -1 = by batch size (default) */
+ *                      SM (throughput: large batches), -1 = by batch size (default)
+ *  SOLO_OPT_FINISH_WARMUP  1 = finish_kernel, launched as a programmatic dependent of the solver,
+ *                      runs one dry pass (no side effects) while the solver drains so that its
+ *                      code and factors are warm for the pass that counts; 0 = off; -1 = by batch
+ *                      size (default: on below 10240 environments) */
 #define SOLO_OPT_GRAPH 1
 #define SOLO_OPT_ZERO_COPY 2
 #define SOLO_OPT_SOLVER_OCCUPANCY 3
+#define SOLO_OPT_FINISH_WARMUP 4
 int solo_set_option(SoloHandle h, int32_t option, int32_t value);
 
 /* Layout of the snapshot buffer bound with solo_bind: per_env = 0 (default) one

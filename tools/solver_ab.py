@@ -23,7 +23,7 @@ cfg = %(cfg)d
 dev = torch.device('cuda', 0)
 env = bench.make_env(cfg, n, dev)
 for name, val in %(opts)r:
-  env.client.set_option({'graph': _abi.OPT_GRAPH, 'zero_copy': _abi.OPT_ZERO_COPY, 'occ': _abi.OPT_SOLVER_OCCUPANCY}[name], val)
+  env.client.set_option({'graph': _abi.OPT_GRAPH, 'zero_copy': _abi.OPT_ZERO_COPY, 'occ': _abi.OPT_SOLVER_OCCUPANCY, 'warm': _abi.OPT_FINISH_WARMUP}[name], val)
 K = bench.CONFIGS[cfg]
 gen = torch.Generator(device=dev).manual_seed(1234)
 acts = [(torch.rand((n, K['n_api']), generator=gen, device=dev) * 2 - 1) * float(K['bound']) for _ in range(64)]
