@@ -25,6 +25,8 @@ class Solo8BaseConfig:
 
   linear_damping: float = .04
   angular_damping: float = .04
+  # accepted and without effect, as in the reference: Bullet combines restitution as the product
+  # of the two bodies' values and the plane's (plane.urdf) is 0
   restitution: float = 0.
   lateral_friction: float = 0.5
 

@@ -349,6 +349,45 @@ def test_action_normalisation_on_the_kernel():
   norm10.close(); raw10.close()
 
 
+def test_fused_program_follows_mutated_plugins():
+  """The fused plan is rebuilt when a registered plug-in changes after the first step
+  (AdditiveReward.add_term, a leaf's margins): the kernel never keeps evaluating a stale program
+  while the Python path sees the new values."""
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  from gym_solo_b200.core import obs, rewards, termination
+  n = 32
+  cfg = Solo8VanillaConfig()
+  cfg.dt = 1.0 / 240.0
+  env = Solo8VanillaEnv(config=cfg, num_envs=n, device='cuda:0')
+  env.obs_factory.register_observation(obs.TorsoIMU(env.robot))
+  add = rewards.AdditiveReward()
+  add.client = env.client
+  flat = rewards.FlatTorsoReward(env.robot, hard_margin=0.01, soft_margin=0.5)
+  add.add_term(1.0, flat)
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    env.reward_factory.register_reward(1, add)
+  env.termination_factory.register_termination(termination.PerpetualTermination())
+  env.reset()
+  model = env._model
+  g = torch.Generator(device='cuda:0').manual_seed(47)
+
+  def step_and_check(expect):
+    act = (torch.rand((n, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    _, r, _, _ = env.step(act)
+    view = so.StateView(env.get_state().double().cpu().numpy(), model)
+    want = expect(view)
+    assert np.abs(r.double().cpu().numpy() - want).max() <= 1e-5
+    assert np.abs(env.reward_factory.get_reward().double().cpu().numpy() - want).max() <= 1e-5   # Python path
+  for _ in range(3):
+    step_and_check(lambda v: so.flat_torso_reward(v, 0.01, 0.5))
+  flat._soft_margin = 3.0                                  # mutate a leaf
+  step_and_check(lambda v: so.flat_torso_reward(v, 0.01, 3.0))
+  add.add_term(-0.5, rewards.UprightReward(env.robot))     # add a term after the first step
+  step_and_check(lambda v: so.flat_torso_reward(v, 0.01, 3.0) - 0.5 * so.upright_reward(v))
+  env.close()
+
+
 def test_episode_statistics_against_a_host_tally():
   """episode_statistics() -> sharding.summarize(): mean return and mean length of the FINISHED
   episodes against a tally kept on the host, three episodes per environment (auto reset), one

@@ -252,3 +252,37 @@ def test_spaces_box_is_float32_like_gym():
   b = spaces.Box(-2 * np.pi, 2 * np.pi, shape=(12,))
   assert b.low.dtype == np.float32 and b.shape == (12,)
   assert float(b.high[0]) == 6.2831854820251465      # float32(2 pi), SURVEY D5
+
+
+# ---- program epoch: what the env's fused-plan cache is keyed on (core/_epoch.py) --------------
+def test_program_epoch_moves_on_every_change_that_a_fused_program_bakes_in():
+  from gym_solo_b200.core import _epoch
+  c = FakeClient()
+
+  def moved(fn):
+    before = _epoch.value
+    fn()
+    return _epoch.value != before
+
+  of = obs.ObservationFactory(c)
+  assert moved(lambda: of.register_observation(testing.CompliantObs(None)))
+  rf = rewards.RewardFactory(c)
+  flat = rewards.FlatTorsoReward(1, hard_margin=.1, soft_margin=1.)
+  with warnings.catch_warnings():
+    warnings.simplefilter('ignore', DeprecationWarning)
+    assert moved(lambda: rf.register_reward(1, flat))
+  add = rewards.AdditiveReward()
+  add.client = c
+  assert moved(lambda: add.add_term(0.5, rewards.UprightReward(1)))      # add_term after the first step
+  assert moved(lambda: setattr(flat, '_soft_margin', 2.))                # a leaf's margins
+  tb = terms.TimeBasedTermination(10)
+  tf = terms.TerminationFactory()
+  assert moved(lambda: tf.register_termination(tb))
+  assert moved(lambda: setattr(tb, 'max_step_delta', 20))
+  enc = obs.MotorEncoder(1, max_rotation=2.)
+  assert moved(lambda: setattr(enc, '_max_rot', 3.))
+  # reading does not move it
+  assert not moved(lambda: (flat._soft_margin, tb.max_step_delta, rf.fused_ops()))
+  # the mutated values are what the next compiled program carries
+  ops = rf.fused_ops()
+  assert any(abs(o.p[1] - 2.0) < 1e-12 for o in ops if o.op == _abi.REW_FLAT_TORSO)

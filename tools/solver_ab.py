@@ -21,6 +21,12 @@ from gym_solo_b200 import _abi
 n = %(n)d
 cfg = %(cfg)d
 dev = torch.device('cuda', 0)
+blob_override = [v for k, v in %(sopts)r if k == 'blob']
+if blob_override:
+  # another compiled model for the same workload (e.g. round 1's support-point sets)
+  import gym_solo_b200.assets as _A
+  _orig = _A.blob_for_urdf
+  _A.blob_for_urdf = lambda p: os.path.abspath(blob_override[0]) if 'solo8v2' in p else _orig(p)
 env = bench.make_env(cfg, n, dev)
 for name, val in %(opts)r:
   env.client.set_option({'graph': _abi.OPT_GRAPH, 'zero_copy': _abi.OPT_ZERO_COPY, 'occ': _abi.OPT_SOLVER_OCCUPANCY, 'warm': _abi.OPT_FINISH_WARMUP}[name], val)
@@ -75,8 +81,10 @@ def main():
   for n in sizes:
     for spec in libs:
       lib, *rest = spec.split('@')
-      opts = [(x.split('=')[0], int(x.split('=')[1])) for x in rest]
-      code = CHILD % dict(root=ROOT, lib='' if lib == 'product' else os.path.abspath(lib), n=n, cfg=cfg, opts=opts)
+      opts = [(x.split('=')[0], int(x.split('=')[1])) for x in rest if not x.startswith('blob=')]
+      sopts = [(x.split('=')[0], x.split('=', 1)[1]) for x in rest if x.startswith('blob=')]
+      code = CHILD % dict(root=ROOT, lib='' if lib == 'product' else os.path.abspath(lib), n=n, cfg=cfg, opts=opts,
+                          sopts=sopts)
       r = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True)
       line = r.stdout.strip().splitlines()[-1] if r.stdout.strip() else 'FAILED: ' + r.stderr[-400:]
       print(n, spec, line, flush=True)
