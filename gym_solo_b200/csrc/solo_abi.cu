@@ -28,7 +28,7 @@ struct SoloHandle_ {
   int obs_dim;
   bool legpar;            // setup phase with one lane per (environment, leg): latency-bound batch sizes
   int block;              // threads per block of the one-thread-per-env kernels
-  bool solve_hiocc;       // solver instantiation held to 14 blocks per SM (throughput-bound batch sizes)
+  bool solve_hiocc;       // 128-register solver instantiation, 13 blocks per SM (throughput-bound batch sizes)
   bool warm_finish;       // finish_kernel runs a dry pass behind the solver (small batches: fetch bound)
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
@@ -289,7 +289,7 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   }
   // Up to a few waves of solver blocks the launch lasts as long as its slowest environment and the
   // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
-  // and 14 instead of 12 resident warps per SM win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
+  // and 13 instead of 12 resident warps per SM (128 registers; shared memory is then the limit) win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
   h->solve_hiocc = n_envs >= kHiOccEnvs;
   h->warm_finish = n_envs < kHiOccEnvs;
   h->motor_mask = 0;

@@ -45,7 +45,7 @@ constexpr int kMaxApi = 16;
 constexpr int kMaxCand = 128;
 // simultaneous contact points per environment (SoloConfig.max_contacts <= this): the solver
 // warp's shared-memory array of active contacts is sized by it, and 56 entries (16 KB per block
-// with the record) let 14 one-warp blocks share an SM
+// with the record) let 13 one-warp blocks share an SM
 constexpr int kMaxContacts = 56;
 constexpr int kStateBase = 13;
 constexpr int kMaxObsTerms = 8;

@@ -410,8 +410,8 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
 
 // MINB: minimum resident blocks per SM the register allocation is held to.  0 = whatever the
 // solve needs (166 registers, 12 blocks per SM): fastest for one environment's chain, i.e. for
-// batches whose launch is its slowest environment.  14 = 144 registers (a few spills): 14
-// blocks per SM, the better trade once the launch is throughput bound (large batches).
+// batches whose launch is its slowest environment.  14 = 128 registers (240 bytes of spills): 13
+// blocks per SM (shared memory then limits), the better trade once the launch is throughput bound (large batches).
 template <int CH, bool DBG, int MINB>
 __global__ void __launch_bounds__(32, MINB)
 solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const uint32_t motor_mask,

@@ -239,7 +239,7 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  *                      set of output buffers instead of 3 x num_substeps launches
  *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies
  *  SOLO_OPT_SOLVER_OCCUPANCY  which build of the solver kernel runs: 0 = 166 registers / 12
- *                      blocks per SM (latency: small batches), 1 = 144 registers / 14 blocks per
+ *                      blocks per SM (latency: small batches), 1 = 128 registers / 13 blocks per
  *                      SM (throughput: large batches), -1 = by batch size (default)
  *  SOLO_OPT_FINISH_WARMUP  1 = finish_kernel, launched as a programmatic dependent of the solver,
  *                      runs one dry pass (no side effects) while the solver drains so that its
