@@ -490,8 +490,8 @@ def main():
     }
     if world == 1 and not args.no_cpu_baseline:
       threads = os.cpu_count() or 1
-      # ~10 s of host work on all threads
-      c_envs, c_steps = (2048, 1200 // (2 * sub)) if args.config != 3 else (2048, 400)
+      # ~10 s of host work on all threads (3.4e5 / 2.1e5 / 1.5e5 / 0.7e5 env-steps/s on the 16-thread box)
+      c_envs, c_steps = {1: (2048, 1600), 2: (2048, 1000), 3: (2048, 750), 4: (2048, 350)}[args.config]
       cv, ct = run_cpu(args.config, c_envs, c_steps, 2, threads)
       line['cpu_baseline'] = {'value': cv, 'unit': UNIT, 'cores': threads, 'kind': 'port',
                               'cpu_model': cpu_model_name(),

@@ -630,7 +630,8 @@ static StepGraph *capture_step(SoloHandle h, const float *actions_dev, float act
 }
 
 static int step_impl(SoloHandle h, const float *actions_dev, float action_scale, float *obs_dev, float *reward_dev,
-                     uint8_t *done_dev, float *terminal_obs_dev, cudaStream_t st) {
+                     uint8_t *done_dev, float *terminal_obs_dev, cudaStream_t st, cudaStream_t *ran = nullptr) {
+  if (ran) *ran = st;
   if (!h->use_graph || h->timing) return step_launches(h, actions_dev, action_scale, obs_dev, reward_dev, done_dev, terminal_obs_dev, st);
   // retire graphs captured under older bindings / programs
   if (!h->graphs.empty() && h->graphs[0]->epoch != h->epoch) drop_graphs(h);
@@ -681,6 +682,7 @@ static int step_impl(SoloHandle h, const float *actions_dev, float action_scale,
     g->actions = actions_dev;
   }
   g->used = ++tick;
+  if (ran) *ran = run;
   cudaError_t e = cudaGraphLaunch(g->exec, run);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaGraphLaunch");
   h->launches += 3 * (int64_t)h->K.C.substeps;
@@ -757,11 +759,12 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale, 
   }
   void *act_dev = device_alias(actions_host);
   if (h->zero_copy && act_dev && h->map_dev[0] && h->map_dev[1] && h->map_dev[2]) {
+    cudaStream_t ran = st;
     int rc = step_impl(h, (const float *)act_dev, action_scale, (float *)h->map_dev[0], (float *)h->map_dev[1],
-                       (uint8_t *)h->map_dev[2], nullptr, st);
+                       (uint8_t *)h->map_dev[2], nullptr, st, &ran);
     if (rc) return rc;
-    // (a replay on our own blocking stream is ordered before anything later in the legacy stream)
-    cudaError_t e = cudaStreamSynchronize(st);
+    // the stream the step actually ran on (our own blocking stream when the caller's is the legacy one)
+    cudaError_t e = cudaStreamSynchronize(ran);
     if (e != cudaSuccess) return cuda_fail(h, e, "step (asynchronous fault in setup / solve / finish)");
     return SOLO_OK;
   }
