@@ -137,6 +137,27 @@ __device__ __forceinline__ void tile_gather(const float *__restrict__ g, int64_t
   }
   __syncthreads();
 }
+// The same gather without waiting for it: every element goes global -> shared memory as a 4-byte
+// cp.async; tile_gather_wait() before the first read.  The setup kernel issues it first thing and
+// needs the actions only for the motor rows at its very end, so the latency of the action bytes
+// (over PCIe when the caller's page-locked buffer is read in place) hides behind the dynamics.
+__device__ __forceinline__ void tile_gather_async(const float *__restrict__ g, int64_t env0, int n_valid, int k,
+                                                  float *sm) {
+  const int ps = pad_stride(k);
+  const int total = n_valid * k;
+  const float *src = g + env0 * k;
+  const float inv_k = 1.f / (float)k;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int r = tile_row(i, inv_k), c = i - r * k;
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(sm + r * ps + c);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + i) : "memory");
+  }
+}
+__device__ __forceinline__ void tile_gather_wait() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncthreads();
+}
+
 __device__ __forceinline__ void tile_scatter(float *__restrict__ g, int64_t env0, int n_valid, int k,
                                              const float *sm, const bool commit = true) {
   const int ps = pad_stride(k);

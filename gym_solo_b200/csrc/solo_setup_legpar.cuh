@@ -69,15 +69,22 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
     q[j] = act[j] ? src[(kStateBase + d) * st] : 0.f;
     qd[j] = act[j] ? src[(kStateBase + M.ndof + d) * st] : 0.f;
   }
+  // ---- actions: [env][n_api] tile -> shared memory, asynchronously.  Torque control needs them in
+  // the bias forces below; position control only in the motor rows at the very end ----
   float cmd[CH];
-  {
-    const float *a = actions;
-    if (!broadcast) {
-      tile_gather(actions, env0, n_valid, n_api, smem);
-      a = smem + (live ? slot : 0) * pad_stride(n_api);
-    }
+  const bool cmd_late = !broadcast && C.control_mode == 0;
+  auto read_cmd = [&]() {
+    const float *a = broadcast ? actions : smem + (live ? slot : 0) * pad_stride(n_api);
 #pragma unroll
     for (int j = 0; j < CH; j++) cmd[j] = act[j] ? a[M.dof_api[M.dof0[l] + j]] * action_scale : 0.f;
+  };
+  if (!broadcast) tile_gather_async(actions, env0, n_valid, n_api, smem);
+  if (!cmd_late) {
+    if (!broadcast) tile_gather_wait();
+    read_cmd();
+  } else {
+#pragma unroll
+    for (int j = 0; j < CH; j++) cmd[j] = 0.f;
   }
   const float base_scale = B.base_mass_scale ? B.base_mass_scale[env] : 1.f;
 
@@ -314,6 +321,10 @@ setup_legpar_kernel(const __grid_constant__ KParams K, const Buffers B, const fl
   // TMA) issued by one thread, instead of 328 scattered 4-byte stores per environment whose queue
   // (lg_throttle) the four lanes would wait on.
   float *rec = smem + ((epb * pad_stride(n_api) + 3) & ~3);
+  if (cmd_late) {
+    tile_gather_wait();
+    read_cmd();
+  }
   if (live) {
 
   // ---- factors for finish_step (FactorLayout) ----
