@@ -888,7 +888,10 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
   R.n_tri = h->n_tri;
   R.env_begin = env_begin;
   R.env_count = env_count;
-  const int tiles_x = (cam->width + kTileW - 1) / kTileW;
+  // one frame alone needs every block it can get (32-pixel tiles, one pixel per thread); a batch of
+  // frames fills the GPU anyway (128-pixel tiles, four pixels per thread, four tiles per block)
+  const int pix = env_count >= 32 ? 4 : 1;
+  const int tiles_x = (cam->width + kTileW * pix - 1) / (kTileW * pix);
   const int tiles_y = (cam->height + kTileH - 1) / kTileH;
   DeviceGuard g(h->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -903,10 +906,10 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
     int rc = check_launch(h, "render_project_kernel");
     if (rc) return rc;
   }
-  // one frame alone needs every block it can get; a batch of frames fills the GPU anyway
   R.tiles_per_block = env_count >= 32 ? 4 : 1;
   const dim3 grid(tiles_x, (tiles_y + R.tiles_per_block - 1) / R.tiles_per_block, env_count);
-  render_raster_kernel<<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
+  if (pix == 4) render_raster_kernel<4><<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
+  else render_raster_kernel<1><<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
   return check_launch(h, "render_raster_kernel");
 }
 

@@ -10,12 +10,12 @@
 //                  the block, shared memory), vertices to pixel coordinates,
 //                  flat Lambert shade, back-face cull; one 64-byte TriRec per
 //                  triangle (affine barycentric and depth equations) plus the robot's screen bounding box per environment.
-//   render_raster_kernel   one block per (32 x 8 pixel tile, environment): the
-//                  block culls the environment's triangles against its tile 256
-//                  at a time (ballot compaction into shared memory), every thread
-//                  depth-tests its pixel against the survivors, then against the
-//                  analytic ground plane z = 0 (checkerboard); one coalesced
-//                  128-byte row of RGBA per warp.
+//   render_raster_kernel   one block per (128 x 8 pixel tile, environment), four
+//                  pixels per thread 32 apart in x: the block culls the environment's
+//                  triangles against its tile 256 at a time (ballot compaction into
+//                  shared memory), every thread depth-tests its pixels against the
+//                  survivors, then against the analytic ground plane z = 0
+//                  (checkerboard); every store of a warp is one 128-byte piece of a row.
 //
 // HBM traffic per frame: the 4 W H output bytes; the TriRec table (64 B x
 // n_tri per environment) is written once and re-read from L2 by the tiles inside
@@ -168,22 +168,41 @@ render_project_kernel(const __grid_constant__ ModelT<float> M, const __grid_cons
   recs[(int64_t)slot * R.n_tri + tri] = rec;
 }
 
+// kPix pixels per thread, 32 apart in x: every store instruction of a warp is one contiguous
+// 128-byte piece of an image row, the per-thread and per-tile bookkeeping is paid once for four
+// pixels, and the four pixels' arithmetic is independent work for the scheduler.
+// (One pixel per thread = 32-pixel-wide tiles for a handful of frames, which need every block
+// they can get; four for batches.)
+template <int kPix>
 __global__ void __launch_bounds__(kRasterThreads)
 render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__restrict__ recs,
                      const int32_t *__restrict__ bbox, uint32_t *__restrict__ out, float *__restrict__ depth_out,
                      int32_t *__restrict__ seg_out) {
   __shared__ float4 se[3][kRasterThreads];
   __shared__ uint32_t s_rgba[kRasterThreads];
+  __shared__ int4 s_box[kRasterThreads];   // pixel bounding box of the survivor: x0, x1, y0, y1 (exclusive ends)
   __shared__ int warp_cnt[kRasterThreads / 32];
   const int slot = blockIdx.z;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-  const int tile_x = blockIdx.x;
-  const int px = tile_x * kTileW + lane;
-  const float fx = (float)px + 0.5f;
-  const int tx0 = tile_x * kTileW, tx1 = tx0 + kTileW;
+  const int tx0 = blockIdx.x * (kTileW * kPix), tx1 = tx0 + kTileW * kPix;
   const int4 bb = *reinterpret_cast<const int4 *>(bbox + 4 * slot);
   const TriRec *mine = recs + (int64_t)slot * R.n_tri;
   const int4 *meta0 = reinterpret_cast<const int4 *>(&mine[t < R.n_tri ? t : 0].box_lo);
+  const bool x_touched = bb.x < tx1 && -bb.z > tx0;
+
+  // per-pixel constants of the thread's four columns: pixel centre, and the part of the view ray
+  // that depends on x only (ray = ray_z + nx ray_x + ny ray_y)
+  float fx[kPix], ax[kPix], ay[kPix], az[kPix];
+#pragma unroll
+  for (int k = 0; k < kPix; k++) {
+    fx[k] = (float)(tx0 + lane + kTileW * k) + 0.5f;
+    const float nx = fx[k] * R.ndc_sx - 1.f;
+    ax[k] = R.ray_z[0] + nx * R.ray_x[0];
+    ay[k] = R.ray_z[1] + nx * R.ray_x[1];
+    az[k] = R.ray_z[2] + nx * R.ray_x[2];
+  }
+  // the checkerboard in cell units
+  const float ex = R.eye[0] * R.inv_checker, ey = R.eye[1] * R.inv_checker;
 
   // several vertically adjacent tiles per block when there are many environments: the short
   // sky / plane tiles amortise the block launch
@@ -194,10 +213,12 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
     const int py = ty0 + wid;
     const float fy = (float)py + 0.5f;
 
-    float best = 1.f;                       // ndc depth of the far plane
-    uint32_t colour = R.sky_rgba;
+    float best[kPix];
+    uint32_t colour[kPix];
+#pragma unroll
+    for (int k = 0; k < kPix; k++) { best[k] = 1.f; colour[k] = R.sky_rgba; }   // ndc depth of the far plane
 
-    const bool touched = bb.x < tx1 && -bb.z > tx0 && bb.y < ty1 && -bb.w > ty0;
+    const bool touched = x_touched && bb.y < ty1 && -bb.w > ty0;
     if (touched) {
       int4 m_next = *meta0;
       for (int base = 0; base < R.n_tri; base += kRasterThreads) {
@@ -222,16 +243,30 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
           const float4 *e = mine[idx].e;
           se[0][p] = e[0]; se[1][p] = e[1]; se[2][p] = e[2];
           s_rgba[p] = (uint32_t)m.z;
+          s_box[p] = make_int4(x0, x1, y0, y1);
         }
         __syncthreads();
         for (int k = 0; k < total; k++) {
+          // a warp is one image row and four 32-pixel segments of it: a survivor of the tile whose
+          // box misses the row is skipped for the price of one shared load, a segment it misses
+          // for a compare (all warp-uniform)
+          const int4 bx = s_box[k];
+          if (py < bx.z || py >= bx.w) continue;
           const float4 e0 = se[0][k], e1 = se[1][k], e2 = se[2][k];
-          const float l0 = fmaf(e0.x, fx, fmaf(e0.y, fy, e0.z));
-          const float l1 = fmaf(e1.x, fx, fmaf(e1.y, fy, e1.z));
-          const float l2 = fmaf(e2.x, fx, fmaf(e2.y, fy, e2.z));
-          if (fminf(l0, fminf(l1, l2)) >= 0.f) {
-            const float z = fmaf(e0.w, fx, fmaf(e1.w, fy, e2.w));
-            if (z < best && z >= -1.f) { best = z; colour = s_rgba[k]; }
+          const uint32_t c = s_rgba[k];
+          // the row part of the four affine forms once, the column part per pixel
+          const float r0 = fmaf(e0.y, fy, e0.z), r1 = fmaf(e1.y, fy, e1.z), r2 = fmaf(e2.y, fy, e2.z);
+          const float rz = fmaf(e1.w, fy, e2.w);
+#pragma unroll
+          for (int q = 0; q < kPix; q++) {
+            const int sx0 = tx0 + kTileW * q;
+            if (bx.x < sx0 + kTileW && bx.y > sx0) {
+              const float l0 = fmaf(e0.x, fx[q], r0), l1 = fmaf(e1.x, fx[q], r1), l2 = fmaf(e2.x, fx[q], r2);
+              if (fminf(l0, fminf(l1, l2)) >= 0.f) {
+                const float z = fmaf(e0.w, fx[q], rz);
+                if (z < best[q] && z >= -1.f) { best[q] = z; colour[q] = c; }
+              }
+            }
           }
         }
         __syncthreads();
@@ -239,29 +274,33 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
     }
 
     // ground plane z = 0 (plane.urdf, solo8_base_env.py:47): analytic ray hit, checkerboard
-    const bool on_robot = best < 1.f;   // a triangle won so far
-    bool on_plane = false;
-    {
-      const float nx = fx * R.ndc_sx - 1.f, ny = 1.f - fy * R.ndc_sy;
-      const float rz = R.ray_z[2] + nx * R.ray_x[2] + ny * R.ray_y[2];
-      const float tt = -R.eye[2] / rz;
+    const float ny = 1.f - fy * R.ndc_sy;
+    const float by = ny * R.ray_y[0], cy = ny * R.ray_y[1], dy = ny * R.ray_y[2];
+    const bool row_ok = py < R.height;
+    const int64_t row = ((int64_t)slot * R.height + py) * R.width;
+#pragma unroll
+    for (int k = 0; k < kPix; k++) {
+      const bool on_robot = best[k] < 1.f;   // a triangle won so far
+      bool on_plane = false;
+      const float rz = az[k] + dy;
+      const float tt = __fdividef(-R.eye[2], rz);
       const float z = -R.depth_a + R.plane_k * rz;
-      if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best) {
-        best = z;
+      if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best[k]) {
+        best[k] = z;
         on_plane = true;
-        const float hx = R.eye[0] + tt * (R.ray_z[0] + nx * R.ray_x[0] + ny * R.ray_y[0]);
-        const float hy = R.eye[1] + tt * (R.ray_z[1] + nx * R.ray_x[1] + ny * R.ray_y[1]);
-        const int cell = (int)floorf(hx * R.inv_checker) + (int)floorf(hy * R.inv_checker);
-        colour = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
+        const float tc = tt * R.inv_checker;
+        const int cell = __float2int_rd(fmaf(tc, ax[k] + by, ex)) + __float2int_rd(fmaf(tc, ay[k] + cy, ey));
+        colour[k] = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
       }
-    }
-    if (px < R.width && py < R.height) {
-      const int64_t pix = ((int64_t)slot * R.height + py) * R.width + px;
-      out[pix] = colour;
-      // getCameraImage's other two images: OpenGL depth in [0, 1] (1 = far plane / nothing hit) and
-      // the body id (plane 0, robot 1, nothing -1)
-      if (depth_out) depth_out[pix] = 0.5f * best + 0.5f;
-      if (seg_out) seg_out[pix] = on_plane ? 0 : (on_robot ? 1 : -1);
+      const int px = tx0 + lane + kTileW * k;
+      if (row_ok && px < R.width) {
+        const int64_t pix = row + px;
+        out[pix] = colour[k];
+        // getCameraImage's other two images: OpenGL depth in [0, 1] (1 = far plane / nothing hit) and
+        // the body id (plane 0, robot 1, nothing -1)
+        if (depth_out) depth_out[pix] = 0.5f * best[k] + 0.5f;
+        if (seg_out) seg_out[pix] = on_plane ? 0 : (on_robot ? 1 : -1);
+      }
     }
   }
 }
