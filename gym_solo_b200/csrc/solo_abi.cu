@@ -908,8 +908,11 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
   }
   R.tiles_per_block = env_count >= 32 ? 4 : 1;
   const dim3 grid(tiles_x, (tiles_y + R.tiles_per_block - 1) / R.tiles_per_block, env_count);
-  if (pix == 4) render_raster_kernel<4><<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
-  else render_raster_kernel<1><<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev);
+  const bool aux = depth_dev || seg_dev;
+#define SOLO_RASTER(P, A) render_raster_kernel<P, A><<<grid, kRasterThreads, 0, st>>>(R, recs, bbox, (uint32_t *)rgba_dev, depth_dev, seg_dev)
+  if (pix == 4) { if (aux) SOLO_RASTER(4, true); else SOLO_RASTER(4, false); }
+  else { if (aux) SOLO_RASTER(1, true); else SOLO_RASTER(1, false); }
+#undef SOLO_RASTER
   return check_launch(h, "render_raster_kernel");
 }
 

@@ -173,7 +173,9 @@ render_project_kernel(const __grid_constant__ ModelT<float> M, const __grid_cons
 // pixels, and the four pixels' arithmetic is independent work for the scheduler.
 // (One pixel per thread = 32-pixel-wide tiles for a handful of frames, which need every block
 // they can get; four for batches.)
-template <int kPix>
+// AUX: also write getCameraImage's depth buffer and segmentation mask (render() itself discards
+// them, like the reference).
+template <int kPix, bool AUX>
 __global__ void __launch_bounds__(kRasterThreads)
 render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__restrict__ recs,
                      const int32_t *__restrict__ bbox, uint32_t *__restrict__ out, float *__restrict__ depth_out,
@@ -201,8 +203,12 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
     ay[k] = R.ray_z[1] + nx * R.ray_x[1];
     az[k] = R.ray_z[2] + nx * R.ray_x[2];
   }
-  // the checkerboard in cell units
-  const float ex = R.eye[0] * R.inv_checker, ey = R.eye[1] * R.inv_checker;
+  // The checkerboard in cell units.  floor() by the magic-number add: for |c| < 2^21 the float
+  // (c - 0.5) + 1.5 * 2^23 is an integer with floor(c) in the low bits of its mantissa
+  // (conversions run at an eighth of the FMA rate, and there would be two per pixel); only the
+  // parity of the two floors is needed.
+  constexpr float kMagic = 12582912.f;
+  const float ex = R.eye[0] * R.inv_checker - 0.5f, ey = R.eye[1] * R.inv_checker - 0.5f;
 
   // several vertically adjacent tiles per block when there are many environments: the short
   // sky / plane tiles amortise the block launch
@@ -277,7 +283,8 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
     const float ny = 1.f - fy * R.ndc_sy;
     const float by = ny * R.ray_y[0], cy = ny * R.ray_y[1], dy = ny * R.ray_y[2];
     const bool row_ok = py < R.height;
-    const int64_t row = ((int64_t)slot * R.height + py) * R.width;
+    const int64_t row = ((int64_t)slot * R.height + py) * R.width + tx0 + lane;
+    uint32_t *out_row = out + row;
 #pragma unroll
     for (int k = 0; k < kPix; k++) {
       const bool on_robot = best[k] < 1.f;   // a triangle won so far
@@ -288,18 +295,18 @@ render_raster_kernel(const __grid_constant__ RenderParams R, const TriRec *__res
       if (rz != 0.f && tt > R.near_t && tt < R.far_t && z < best[k]) {
         best[k] = z;
         on_plane = true;
-        const float tc = tt * R.inv_checker;
-        const int cell = __float2int_rd(fmaf(tc, ax[k] + by, ex)) + __float2int_rd(fmaf(tc, ay[k] + cy, ey));
-        colour[k] = (cell & 1) ? R.plane_rgba_b : R.plane_rgba_a;
+        const float tc = fminf(tt * R.inv_checker, 2.0e6f);      // (cells beyond 2 million: keep the magic add exact)
+        const float ca = fmaf(tc, ax[k] + by, ex) + kMagic, cb = fmaf(tc, ay[k] + cy, ey) + kMagic;
+        colour[k] = ((__float_as_int(ca) ^ __float_as_int(cb)) & 1) ? R.plane_rgba_b : R.plane_rgba_a;
       }
-      const int px = tx0 + lane + kTileW * k;
-      if (row_ok && px < R.width) {
-        const int64_t pix = row + px;
-        out[pix] = colour[k];
-        // getCameraImage's other two images: OpenGL depth in [0, 1] (1 = far plane / nothing hit) and
-        // the body id (plane 0, robot 1, nothing -1)
-        if (depth_out) depth_out[pix] = 0.5f * best[k] + 0.5f;
-        if (seg_out) seg_out[pix] = on_plane ? 0 : (on_robot ? 1 : -1);
+      if (row_ok && tx0 + lane + kTileW * k < R.width) {
+        out_row[kTileW * k] = colour[k];
+        if (AUX) {
+          // getCameraImage's other two images: OpenGL depth in [0, 1] (1 = far plane / nothing hit)
+          // and the body id (plane 0, robot 1, nothing -1)
+          if (depth_out) depth_out[row + kTileW * k] = 0.5f * best[k] + 0.5f;
+          if (seg_out) seg_out[row + kTileW * k] = on_plane ? 0 : (on_robot ? 1 : -1);
+        }
       }
     }
   }
