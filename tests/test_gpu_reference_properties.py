@@ -308,3 +308,65 @@ def test_pgs_iteration_counts_match_the_oracle():
     assert (np.abs(diff) <= 1).mean() >= 0.97, dict(zip(vals.tolist(), cnts.tolist()))
     assert got.sum() <= want.sum() * 1.02 + n     # no float32 tail of extra iterations
     c.disconnect()
+
+
+# ---- the rest of gym_solo/envs/test_solo8v2vanilla.py, through the drop-in surface -------
+@pytest.mark.parametrize('limit', [2 * np.pi, 1.5])
+def test_action_space_follows_the_configured_limit(limit):
+  """test_solo8v2vanilla.py:55-64: 12 joints (8 dof + 4 fixed ankles), +-max_motor_rotation."""
+  from gym_solo_b200 import spaces
+  from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
+  config = Solo8VanillaConfig(max_motor_rotation=limit, motor_torque_limit=limit)
+  env = Solo8VanillaEnv(config=config, device='cuda:0')
+  assert env.action_space == spaces.Box(-limit, limit, shape=(12,))
+  assert env.action_space.sample().shape == (12,)
+  env._close()
+
+
+def test_normalized_and_invalid_action_space():
+  """test_solo8v2vanilla.py:66-74."""
+  from gym_solo_b200 import spaces
+  env = _reference_env(1, normalize_actions=True)
+  assert env.action_space == spaces.Box(-1, 1, shape=(12,))
+  env._action_space = None
+  with pytest.raises(ValueError):
+    env.action_space
+  env._close()
+
+
+def test_step_with_nothing_registered_is_refused():
+  """test_solo8v2vanilla.py:165-168: a step without rewards raises ValueError."""
+  env = _reference_env(2)
+  with pytest.raises(ValueError):
+    env.step(np.zeros(12))
+  env._close()
+
+
+def test_step_simple_reward_and_result_shapes():
+  """test_solo8v2vanilla.py:170-175: reward == 1 with SimpleReward, on every environment, and
+  the (obs, reward, done, info) tuple of the reference with a leading num_envs axis."""
+  env = _reference_env(3)
+  env.reward_factory.register_reward(1, testing.SimpleReward())
+  env.obs_factory.register_observation(testing.CompliantObs(None))
+  env.termination_factory.register_termination(testing.DummyTermination(0, True))
+  obs, reward, done, info = env.step(env.action_space.sample())
+  assert tuple(obs.shape) == (3, 2) and tuple(reward.shape) == (3,) and tuple(done.shape) == (3,)
+  assert (reward.cpu().numpy() == 1).all()
+  assert done.cpu().numpy().all()              # DummyTermination(0, True) is always done
+  assert 'labels' in info and len(info['labels']) == 2
+  env._close()
+
+
+def test_realtime_sleeps_one_dt_per_step(monkeypatch):
+  """test_solo8v2vanilla.py:37-47: realtime=True sleeps between steps (time.sleep patched out
+  the way the reference's test does)."""
+  import time
+  slept = []
+  monkeypatch.setattr(time, 'sleep', lambda s: slept.append(s))
+  env = _reference_env(1, realtime=True)
+  env.reward_factory.register_reward(1, testing.SimpleReward())
+  env.obs_factory.register_observation(testing.CompliantObs(None))
+  env.termination_factory.register_termination(testing.DummyTermination(0, True))
+  env.step(env.action_space.sample())
+  assert slept and slept[-1] == env.config.dt
+  env._close()
