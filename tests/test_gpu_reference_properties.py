@@ -316,7 +316,8 @@ def test_action_space_follows_the_configured_limit(limit):
   """test_solo8v2vanilla.py:55-64: 12 joints (8 dof + 4 fixed ankles), +-max_motor_rotation."""
   from gym_solo_b200 import spaces
   from gym_solo_b200.envs import Solo8VanillaEnv, Solo8VanillaConfig
-  config = Solo8VanillaConfig(max_motor_rotation=limit, motor_torque_limit=limit)
+  config = Solo8VanillaConfig(motor_torque_limit=limit)
+  config.max_motor_rotation = limit        # a class attribute in the reference too (configs.py:20)
   env = Solo8VanillaEnv(config=config, device='cuda:0')
   assert env.action_space == spaces.Box(-limit, limit, shape=(12,))
   assert env.action_space.sample().shape == (12,)
@@ -349,7 +350,7 @@ def test_step_simple_reward_and_result_shapes():
   env.reward_factory.register_reward(1, testing.SimpleReward())
   env.obs_factory.register_observation(testing.CompliantObs(None))
   env.termination_factory.register_termination(testing.DummyTermination(0, True))
-  obs, reward, done, info = env.step(env.action_space.sample())
+  obs, reward, done, info = env.step(np.stack([env.action_space.sample() for _ in range(3)]))
   assert tuple(obs.shape) == (3, 2) and tuple(reward.shape) == (3,) and tuple(done.shape) == (3,)
   assert (reward.cpu().numpy() == 1).all()
   assert done.cpu().numpy().all()              # DummyTermination(0, True) is always done
