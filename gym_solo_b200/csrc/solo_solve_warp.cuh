@@ -22,8 +22,10 @@
 //     records sorted by contact index: normal row, the friction pair, the three
 //     impulses, and the mask of speculative rows that precede the contact.  The
 //     walk over it is a counted loop: addresses are k * stride, nothing on the
-//     chain but the arithmetic.  A promotion (at most once per contact and solve)
-//     shifts the tail of the array; the owner lane builds the friction pair then;
+//     chain but the arithmetic; the normal rows go through two register buffers,
+//     entry k + 1 loaded while entry k is on the chain.  A promotion (at most once
+//     per contact and solve) shifts the tail of the array; the owner lane builds
+//     the friction pair then;
 //   * friction: both rows on the same velocity, cone projection without a branch.
 #ifndef SOLO_SOLVE_WARP_CUH_
 #define SOLO_SOLVE_WARP_CUH_
@@ -66,6 +68,9 @@ struct WarpSolveSmem {
   float ent[kMaxContacts][ActiveLayout<CH>::kSize];  // active contacts, sorted by contact index
   int32_t list[kMaxContacts];                        // contact -> support point
   float llam[kLegs * CH];                            // scaled joint-limit impulses (rows are rare)
+#ifdef SOLO_SECTION_PROBE
+  long long probe[4];                                // probe build: cycles in normal rows / friction pairs, screens
+#endif
 };
 
 // contact bitmasks: 32 bits when the env has <= 32 contacts (99.8 % of env-steps), else 64
@@ -126,6 +131,11 @@ __device__ __forceinline__ float dense_gap(const float (&r)[N], const float (&y)
     else a3 = fmaf(-r[a], y[a], a3);
   }
   return (a0 + a1) + (a2 + a3);
+}
+template <int W, int N>
+__device__ __forceinline__ void dense_axpy(float (&y)[W], const float (&r)[N], const float d) {
+#pragma unroll
+  for (int a = 0; a < W; a++) y[a] = fmaf(r[a], d, y[a]);
 }
 
 // The owner lane of a promoted contact expands its three rows into entry `e`.
@@ -197,6 +207,14 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   float budget = 0.f;
   int n_act = 0;
   int it = 0;
+#ifdef SOLO_SECTION_PROBE
+  long long pr_n = 0, pr_f = 0, pr_s = 0, pr_t = 0, pr_m = 0, pr_nu = 0, pr_fu = 0;
+#define PROBE_T() do { pr_t = clock64(); } while (0)
+#define PROBE_ADD(x) do { const long long _n = clock64(); x += _n - pr_t; pr_t = _n; } while (0)
+#else
+#define PROBE_T() do { } while (0)
+#define PROBE_ADD(x) do { } while (0)
+#endif
 #ifdef SOLO_IDLE_PROBE
   int probe_visits = 0, probe_idle = 0;   // probe build: how many promoted-contact visits found the contact idle
 #endif
@@ -240,6 +258,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   };
   for (; it < C.iters;) {
     float res = 0.f;
+    PROBE_T();
     if (lim != 0 && (it & 1)) limit_rows(true, res);
     // ---- motor rows (btMultiBodyJointMotor), direction alternates with parity ----
     if (motor_mask != 0) {
@@ -278,96 +297,134 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
       }
     }
     if (lim != 0 && !(it & 1)) limit_rows(false, res);
+    PROBE_ADD(pr_m);
 
     if (nc > 0) {
       // ---- normal rows ----
-      // Entry k of sm.ent is the k-th active contact; its `range` is the set of
-      // speculative rows between the previous active contact and itself.  Before
-      // entry k is updated those rows are screened against the current yh; the
-      // first that has come alive is promoted into slot k and applied.
-      for (int k = 0;;) {
-        const bool at_end = k >= n_act;
-        const float *e = &sm.ent[at_end ? 0 : k][0];
-        float nr[AL::NW];
-        load_row(e, nr);
-        const float4 m0 = *reinterpret_cast<const float4 *>(e + AL::kMeta);
-        const float4 m1 = *reinterpret_cast<const float4 *>(e + AL::kMeta + 4);
-        const mask_t range = at_end ? tail_range : MK::make(__float_as_uint(m1.x), __float_as_uint(m1.y));
-        if (range != 0 && budget <= 0.f) {
-          mask_t viol = 0;
-          float t[NR];
-          float slack = 3.0e38f;
+      // Entry k of sm.ent is the k-th active contact; its `range` is the set of speculative
+      // rows between the previous active contact and itself: they are screened against the
+      // current yh before entry k is updated, and the first that has come alive is promoted
+      // into slot k and applied.  The walk is software-pipelined over two register buffers:
+      // entry k + 1 is loaded while entry k is on the dependent chain, and the entry's own gap
+      // is formed before the (rare) screen is decided -- a screen without a promotion leaves
+      // yh alone, one with a promotion reloads.
+      auto load_n = [&](const int k, float (&n)[AL::NW], float &lam, mask_t &range) {
+        const float *e = &sm.ent[k < kMaxContacts ? k : kMaxContacts - 1][0];
+        load_row(e, n);
+        lam = e[AL::kMeta];
+        range = MK::make(__float_as_uint(e[AL::kMeta + 4]), NR > 1 ? __float_as_uint(e[AL::kMeta + 5]) : 0u);
+      };
+      float t[NR];
+      PROBE_T();
+      auto screen = [&](const mask_t range) -> mask_t {
+#ifdef SOLO_SECTION_PROBE
+        pr_s++;
+#endif
+        mask_t viol = 0;
+        float slack = 3.0e38f;
 #pragma unroll
-          for (int q = 0; q < NR; q++) {
-            float a0 = ub[q], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int q = 0; q < NR; q++) {
+          float a0 = ub[q], a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-            for (int a = 0; a < W; a++) {
-              if ((a & 3) == 0) a0 = fmaf(-ud[q][a], y[a], a0);
-              else if ((a & 3) == 1) a1 = fmaf(-ud[q][a], y[a], a1);
-              else if ((a & 3) == 2) a2 = fmaf(-ud[q][a], y[a], a2);
-              else a3 = fmaf(-ud[q][a], y[a], a3);
-            }
-            t[q] = (a0 + a1) + (a2 + a3);
-            // distance from coming alive, speculative rows only (absent rows sit at 1)
-            if (((act >> (lane + 32 * q)) & 1) == 0) slack = fminf(slack, fmaxf(-t[q], 0.f));
-            viol |= (mask_t)__ballot_sync(FULL, t[q] > 0.f) << (32 * q);
+          for (int a = 0; a < W; a++) {
+            if ((a & 3) == 0) a0 = fmaf(-ud[q][a], y[a], a0);
+            else if ((a & 3) == 1) a1 = fmaf(-ud[q][a], y[a], a1);
+            else if ((a & 3) == 2) a2 = fmaf(-ud[q][a], y[a], a2);
+            else a3 = fmaf(-ud[q][a], y[a], a3);
           }
-          viol &= range;
-          budget = 0.999f * __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(slack)));
-          if (viol != 0) {
-            // ---- promotion of contact v into slot k (rare) ----
-            const int v = MK::first(viol);
-            SOLO_CHECK(v >= 0 && v < nc && ((act >> v) & 1) == 0 && n_act < nc && n_act < kMaxContacts && k <= n_act);
-            float dv = __shfl_sync(FULL, t[0], v & 31);
-            if (NR > 1) {
-              const float d1 = __shfl_sync(FULL, t[NR - 1], v & 31);
-              dv = v < 32 ? dv : d1;
-            }
-            // shift entries [k, n_act) up by one; lane j moves the same words of every entry
-            for (int s = n_act - 1; s >= k; s--)
-              for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
-            __syncwarp();
-            // the owner lane builds the contact's three rows (the friction pair for the first time)
-            if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv, link_mu);
-            act |= MK::bit(v);
-            n_act++;
-            __syncwarp();
-            // ranges of every entry and of the tail
-            for (int s = lane; s < n_act; s += 32) {
-              const int idx = __float_as_int(sm.ent[s][AL::kMeta + 3]);
-              const int prev = s > 0 ? __float_as_int(sm.ent[s - 1][AL::kMeta + 3]) : -1;
-              const mask_t m = MK::below(idx) & ~MK::below(prev + 1);
-              sm.ent[s][AL::kMeta + 4] = __uint_as_float((uint32_t)m);
-              sm.ent[s][AL::kMeta + 5] = __uint_as_float((uint32_t)((uint64_t)m >> 32));
-            }
-            tail_range = all & ~MK::below(MK::last(act) + 1);
-            __syncwarp();
-            float pr[AL::NW];
-            load_row(&sm.ent[k][0], pr);
-#pragma unroll
-            for (int a = 0; a < W; a++) y[a] = fmaf(pr[a], dv, y[a]);
-            const float rr = dv * pr[W + 1];
-            res = fmaxf(res, rr * rr);
-            budget = 0.f;   // a row elsewhere may be alive too: screen again
-            k++;
-            continue;
-          }
+          t[q] = (a0 + a1) + (a2 + a3);
+          // distance from coming alive, speculative rows only (absent rows sit at 1)
+          if (((act >> (lane + 32 * q)) & 1) == 0) slack = fminf(slack, fmaxf(-t[q], 0.f));
+          viol |= (mask_t)__ballot_sync(FULL, t[q] > 0.f) << (32 * q);
         }
-        if (at_end) break;
-        SOLO_CHECK(k >= 0 && k < n_act && __float_as_int(m0.w) >= 0 && __float_as_int(m0.w) < nc &&
-                   ((act >> __float_as_int(m0.w)) & 1) == 1 && (k == 0 || __float_as_int(sm.ent[k - 1][AL::kMeta + 3]) < __float_as_int(m0.w)));
-        const float lam_n = m0.x;
-        const float sum = fmaxf(dense_gap<W>(nr, y, lam_n), 0.f);
-        const float d = sum - lam_n;
+        budget = 0.999f * __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(slack)));
+        return viol & range;
+      };
+      auto update_n = [&](const int k, const float (&n)[AL::NW], const float lam, const float gap) {
+        SOLO_CHECK(k >= 0 && k < n_act);
+#ifdef SOLO_SECTION_PROBE
+        pr_nu++;
+#endif
+        const float sum = fmaxf(gap, 0.f);
+        const float d = sum - lam;
         sm.ent[k][AL::kMeta] = sum;
-#pragma unroll
-        for (int a = 0; a < W; a++) y[a] = fmaf(nr[a], d, y[a]);
-        const float rr = d * nr[W + 1];
+        dense_axpy<W>(y, n, d);
+        const float rr = d * n[W + 1];
         res = fmaxf(res, rr * rr);
         budget -= fabsf(d);
+      };
+      for (int k = 0;;) {
+        mask_t viol = 0;
+        if (k < n_act) {
+          float nA[AL::NW], nB[AL::NW], lamA, lamB;
+          mask_t rA, rB;
+          load_n(k, nA, lamA, rA);
+          for (;;) {
+            // the entry's own gap in front of the decision (which hangs off the previous update's
+            // |d| through the budget): a screen without a promotion leaves yh alone
+            float g = dense_gap<W>(nA, y, lamA);
+            if (rA != 0 && budget <= 0.f) {
+              viol = screen(rA);
+              if (viol != 0) break;
+            }
+            load_n(k + 1, nB, lamB, rB);   // in the update's block: the loads fill its dependency stalls
+            update_n(k, nA, lamA, g);
+            k++;
+            if (k >= n_act) break;
+            g = dense_gap<W>(nB, y, lamB);
+            if (rB != 0 && budget <= 0.f) {
+              viol = screen(rB);
+              if (viol != 0) break;
+            }
+            load_n(k + 1, nA, lamA, rA);
+            update_n(k, nB, lamB, g);
+            k++;
+            if (k >= n_act) break;
+          }
+        }
+        if (viol == 0) {
+          // behind the last active contact
+          if (tail_range != 0 && budget <= 0.f) viol = screen(tail_range);
+          if (viol == 0) break;
+        }
+        // ---- promotion of contact v into slot k (rare) ----
+        const int v = MK::first(viol);
+        SOLO_CHECK(v >= 0 && v < nc && ((act >> v) & 1) == 0 && n_act < nc && n_act < kMaxContacts && k <= n_act);
+        float dv = __shfl_sync(FULL, t[0], v & 31);
+        if (NR > 1) {
+          const float d1 = __shfl_sync(FULL, t[NR - 1], v & 31);
+          dv = v < 32 ? dv : d1;
+        }
+        // shift entries [k, n_act) up by one; lane j moves the same words of every entry
+        for (int s = n_act - 1; s >= k; s--)
+          for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
+        __syncwarp();
+        // the owner lane builds the contact's three rows (the friction pair for the first time)
+        if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv, link_mu);
+        act |= MK::bit(v);
+        n_act++;
+        __syncwarp();
+        // ranges of every entry and of the tail
+        for (int s = lane; s < n_act; s += 32) {
+          const int idx = __float_as_int(sm.ent[s][AL::kMeta + 3]);
+          const int prev = s > 0 ? __float_as_int(sm.ent[s - 1][AL::kMeta + 3]) : -1;
+          const mask_t m = MK::below(idx) & ~MK::below(prev + 1);
+          sm.ent[s][AL::kMeta + 4] = __uint_as_float((uint32_t)m);
+          sm.ent[s][AL::kMeta + 5] = __uint_as_float((uint32_t)((uint64_t)m >> 32));
+        }
+        tail_range = all & ~MK::below(MK::last(act) + 1);
+        __syncwarp();
+        float pr[AL::NW];
+        load_row(&sm.ent[k][0], pr);
+#pragma unroll
+        for (int a = 0; a < W; a++) y[a] = fmaf(pr[a], dv, y[a]);
+        const float rr = dv * pr[W + 1];
+        res = fmaxf(res, rr * rr);
+        budget = 0.f;   // a row elsewhere may be alive too: screen again
         k++;
       }
 
+      PROBE_ADD(pr_n);
       // ---- friction pairs of the contacts that can hold friction ----
       // both rows on the same velocity, radial projection onto the disc of radius
       // mu * lambda_n (resolveConeFrictionConstraintRows)
@@ -383,6 +440,9 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         if (l4.x == 0.f && l4.y == 0.f && l4.z == 0.f) probe_idle++;
 #endif
         if (l4.x == 0.f && l4.y == 0.f && l4.z == 0.f) continue;
+#ifdef SOLO_SECTION_PROBE
+        pr_fu++;
+#endif
         float sa = dense_gap<W>(fa, y, l4.y), sb = dense_gap<W>(fb, y, l4.z);
         const float limit = fa[W + 3] * l4.x;                  // mu * lambda_n, true units
         const float ta = sa * fa[W + 2], tb = sb * fb[W + 2];  // true units
@@ -391,17 +451,21 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         sa *= sc; sb *= sc;
         const float da = sa - l4.y, db = sb - l4.z;
         e[AL::kMeta + 1] = sa; e[AL::kMeta + 2] = sb;
-#pragma unroll
-        for (int a = 0; a < W; a++) y[a] = fmaf(fb[a], db, fmaf(fa[a], da, y[a]));
+        dense_axpy<W>(y, fa, da);
+        dense_axpy<W>(y, fb, db);
         const float r1 = da * fa[W + 1], r2 = db * fb[W + 1];
         res = fmaxf(res, fmaxf(r1 * r1, r2 * r2));
         budget -= fabsf(da) + fabsf(db);
       }
+      PROBE_ADD(pr_f);
     }
     it++;
     if (res <= C.res_thr) break;
   }
   *n_active = n_act;
+#ifdef SOLO_SECTION_PROBE
+  if (lane == 0) { sm.probe[0] = (pr_n / 100) * 1000 + min(999ll, pr_nu); sm.probe[1] = (pr_f / 100) * 1000 + min(999ll, pr_fu); sm.probe[2] = pr_s; sm.probe[3] = pr_m; }
+#endif
 #ifdef SOLO_IDLE_PROBE
   *n_active = n_act + 1000 * (probe_visits > 0 ? (100 * probe_idle) / probe_visits : 0);
 #endif
@@ -499,6 +563,15 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     float *st = B.yh + (int64_t)W * B.n + env;
     st[0] = (float)it; st[(int64_t)B.n] = (float)nc; st[2 * (int64_t)B.n] = (float)n_active;
     st[3 * (int64_t)B.n] = (float)(clock64() - t_begin);
+#ifdef SOLO_SECTION_PROBE
+    // probe build (tools/solver_sections.py): the contact-count rows carry cycles in the normal rows
+    // (low 3 decimal digits: active contacts) and in the friction pairs (low 3 digits: screens / 10)
+    if (it > 0) {
+      st[0] = (float)(it + 100 * (sm.probe[3] / 100));
+      st[(int64_t)B.n] = (float)sm.probe[0];
+      st[2 * (int64_t)B.n] = (float)sm.probe[1];
+    }
+#endif
 #ifdef SOLO_TIMELINE
     {
       // probe build (tools/solver_timeline.py): the contact-count rows carry the block's start

@@ -187,6 +187,9 @@ class Solo8VanillaEnv(Solo8BaseEnv):
 
     obs_values, obs_labels = self.obs_factory.get_obs()
     reward = self.reward_factory.get_reward()
+    if not torch.is_tensor(reward):
+      # a user reward that returns one number (the reference's signature): the same for every env
+      reward = torch.full((c.n,), float(reward), dtype=torch.float32, device=c.device)
     done = self.termination_factory.is_terminated()
     if not torch.is_tensor(done):
       done = torch.full((c.n,), bool(done), dtype=torch.bool, device=c.device)
