@@ -14,6 +14,7 @@ MAX_BODIES = 13
 MAX_API = 16
 MAX_CAND = 128
 MAX_CONTACTS = 56
+RENDER_STATIC_BYTES = 4 * 1024 * 1024   # SOLO_RENDER_STATIC_BYTES (include/solo8_b200.h)
 MAX_OBS_TERMS = 8
 MAX_REWARD_OPS = 32
 MAX_TERM_TERMS = 8

@@ -74,6 +74,8 @@ EXPORTS = {
     'solo_render_scratch_bytes': (C.c_int64, [C.c_void_p, C.c_int32]),
     'solo_render': (C.c_int, [C.c_void_p, C.POINTER(_abi.SoloCamera), C.c_int32, C.c_int32, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'solo_render_static': (C.c_int, [C.c_void_p, C.POINTER(_abi.SoloCamera), C.c_int32, C.c_int32, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 

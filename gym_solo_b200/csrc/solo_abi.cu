@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -917,3 +918,46 @@ int solo_render(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t 
 }
 
 }  // extern "C"
+
+// ---- solo_render_static: render() for callers that cannot allocate device memory ----
+// The projected-triangle records and bounding boxes of one call live in this file-scope array
+// instead of caller scratch.  In host code `g_render_static` is only a stand-in for the symbol:
+// its device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_render_static[SOLO_RENDER_STATIC_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mutex;
+void *g_static_ptr[kMaxStaticDevices] = {};
+}  // namespace
+
+extern "C" int solo_render_static(SoloHandle h, const SoloCamera *cam, int32_t env_begin, int32_t env_count,
+                                  uint8_t *rgba_dev, float *depth_dev, int32_t *seg_dev, void *stream) {
+  if (!h || !cam || !rgba_dev) return fail(h, SOLO_EINVAL, "null argument");
+  if (env_count < 1) return fail(h, SOLO_EINVAL, "solo_render_static: environment range out of bounds");
+  const int64_t need = solo_render_scratch_bytes(h, env_count);
+  if (need > (int64_t)SOLO_RENDER_STATIC_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "solo_render_static: %d environments x %d triangles need %lld bytes of scratch, the static array holds "
+             "%lld (SOLO_RENDER_STATIC_BYTES); render fewer environments per call or use solo_render with caller scratch",
+             (int)env_count, (int)h->n_tri, (long long)need, (long long)SOLO_RENDER_STATIC_BYTES);
+    return fail(h, SOLO_EINVAL, msg);
+  }
+  if (h->device < 0 || h->device >= kMaxStaticDevices) return fail(h, SOLO_EINVAL, "solo_render_static: device index out of range");
+  void *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    scratch = g_static_ptr[h->device];
+    if (!scratch) {
+      DeviceGuard g(h->device);
+      if (!g.ok) return fail(h, SOLO_ECUDA, "cudaSetDevice failed");
+      const cudaError_t e = cudaGetSymbolAddress(&scratch, g_render_static);
+      if (e != cudaSuccess || !scratch) return cuda_fail(h, e, "cudaGetSymbolAddress(g_render_static)");
+      g_static_ptr[h->device] = scratch;
+    }
+  }
+  // the array keeps the previous call's records: solo_render resets the bounding boxes (the only
+  // part read before it is written) with a memset on `stream`; every record read is rewritten first
+  return solo_render(h, cam, env_begin, env_count, rgba_dev, depth_dev, seg_dev, scratch, stream);
+}

@@ -300,6 +300,21 @@ int solo_bind_mesh(SoloHandle h, const int32_t *tri_body_dev, const float *tri_v
 int64_t solo_render_scratch_bytes(SoloHandle h, int32_t env_count);
 int solo_render(SoloHandle h, const SoloCamera *camera, int32_t env_begin, int32_t env_count,
                 uint8_t *rgba_dev, float *depth_dev, int32_t *seg_dev, void *scratch_dev, void *stream);
+/* solo_render without caller scratch and without any device allocation.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same images as
+ * solo_render (the same two kernels); the projected-triangle records and bounding boxes live in a
+ * file-scope `static __device__` array of SOLO_RENDER_STATIC_BYTES that every GPU loading the
+ * library holds until exit.  A call whose solo_render_scratch_bytes(h, env_count) exceeds that
+ * (59 environments of the 1100-triangle solo8v2 mesh) fails with SOLO_EINVAL and says so in
+ * solo_last_error.  Calls no cudaMalloc, cudaFree or other allocating routine; the first call on a device
+ * resolves the array's address (cudaGetSymbolAddress) -- make it before a graph capture.  Every
+ * call on a device shares the array, which keeps the last call's contents (what must start clean
+ * is reset on `stream` inside the call): calls that overlap on the GPU -- different streams,
+ * different handles -- race; order them. */
+#define SOLO_RENDER_STATIC_BYTES (4 * 1024 * 1024)
+int solo_render_static(SoloHandle h, const SoloCamera *camera, int32_t env_begin, int32_t env_count,
+                       uint8_t *rgba_dev, float *depth_dev, int32_t *seg_dev, void *stream);
 /* Live per-kernel timing (bench.py roofline): while enabled every physics step
  * records CUDA events on the launching stream around its three kernels;
  * solo_phase_times synchronises on them and returns the number of physics
