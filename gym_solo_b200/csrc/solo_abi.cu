@@ -29,7 +29,9 @@ struct SoloHandle_ {
   int obs_dim;
   bool legpar;            // setup phase with one lane per (environment, leg): latency-bound batch sizes
   int block;              // threads per block of the one-thread-per-env kernels
-  bool solve_hiocc;       // 128-register solver instantiation, 13 blocks per SM (throughput-bound batch sizes)
+  int persist_grid;       // grid of the persistent solver build: one resident wave of one-warp blocks
+  int solve_mode;         // solver build: 0 = one block per env, 168 registers; 1 = one block per env, 128 registers
+                          // (13 blocks per SM); 2 = persistent warps (SOLO_OPT_SOLVER_OCCUPANCY)
   bool warm_finish;       // finish_kernel runs a dry pass behind the solver (small batches: fetch bound)
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
@@ -103,11 +105,15 @@ static int pick_block(int n_envs) {
 }
 
 constexpr int kHiOccEnvs = 10240;   // measured crossover between 8192 (-1.4 %) and 12288 (+1.3 %) environments
+#ifndef SOLO_PERSIST_ENVS
+#define SOLO_PERSIST_ENVS 32768      // from here the persistent solver build (measured: even at 32768, -7 % at 65536)
+#endif
+static int auto_solve_mode(int n) { return n >= SOLO_PERSIST_ENVS ? 2 : n >= kHiOccEnvs ? 1 : 0; }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct ScratchLayout {
-  size_t cand, yh, fac, kin, total;
+  size_t cand, yh, fac, kin, work, total;
 };
 static ScratchLayout scratch_layout(const SoloHandle h) {
   const size_t n = (size_t)h->B.n;
@@ -119,6 +125,7 @@ static ScratchLayout scratch_layout(const SoloHandle h) {
   L.yh = off;   off = align256(off + sizeof(float) * (6 + kLegs * h->ch + 4) * n);
   L.fac = off;  off = align256(off + sizeof(float) * facs * n);
   L.kin = off;  off = align256(off + sizeof(float) * kins * n);
+  L.work = off; off = align256(off + 2 * sizeof(int32_t));
   L.total = off;
   return L;
 }
@@ -210,6 +217,22 @@ static cudaError_t launch_ex(void (*kernel)(KArgs...), int grid, int block, size
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
+// One resident wave of the persistent solver build (what the occupancy calculator says fits, times
+// the SM count), or one block per environment when that is fewer.
+template <int CH>
+static int persist_grid(SoloHandle h) {
+  if (h->persist_grid == 0) {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_warp_kernel<CH, false, 0, true>, 32, 0) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || per_sm < 1 || sms < 1) {
+      cudaGetLastError();
+      per_sm = 12; sms = 148;
+    }
+    h->persist_grid = per_sm * sms;
+  }
+  return h->B.n < h->persist_grid ? h->B.n : h->persist_grid;
+}
+
 // Argument block of one captured setup node (cudaGraphExecKernelNodeSetParams wants every
 // argument again when one changes).
 struct SetupArgs {
@@ -291,7 +314,8 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   // Up to a few waves of solver blocks the launch lasts as long as its slowest environment and the
   // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
   // and 13 instead of 12 resident warps per SM (128 registers; shared memory is then the limit) win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
-  h->solve_hiocc = n_envs >= kHiOccEnvs;
+  h->solve_mode = auto_solve_mode(n_envs);
+  h->persist_grid = 0;
   h->warm_finish = n_envs < kHiOccEnvs;
   h->motor_mask = 0;
   if (config->control_mode == SOLO_CONTROL_POSITION)
@@ -394,6 +418,7 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
     h->B.yh = (float *)(base + L.yh);
     h->B.fac = (float *)(base + L.fac);
     h->B.kin = (float *)(base + L.kin);
+    h->B.work = (int32_t *)(base + L.work);
     // support-point table of the solver warp: xyz, friction, leg (-1 base), depth in the chain
     std::vector<float> tab_v(kCandStride * kMaxCand, 0.f);   // per call: handles may be bound from several threads
     float *tab = tab_v.data();
@@ -412,6 +437,8 @@ int solo_bind(SoloHandle h, float *state_dev, int32_t *counters_dev, float *snap
     DeviceGuard g(h->device);
     cudaError_t e = cudaMemcpy(base + L.cand, tab, sizeof(float) * tab_v.size(), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return cuda_fail(h, e, "upload of the support-point table");
+    e = cudaMemset(base + L.work, 0, 2 * sizeof(int32_t));   // the persistent solver's counters rest at zero
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemset of the solver's work counters");
   }
   touch(h);
   h->B.state = state_dev;
@@ -518,12 +545,14 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
     SOLO_SETUP_LAUNCH(CH);                                                                                        \
     if ((rc = check_launch(h, "setup_kernel"))) return rc;                                                        \
     SOLO_MARK(1);                                                                                                 \
-    if (dbg) launch_ex(solve_warp_kernel<CH, true, 0>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,  \
-                       n_cand, margin);                                                                           \
-    else if (h->solve_hiocc) launch_ex(solve_warp_kernel<CH, false, 14>, h->B.n, 32, 0, st, pdl, h->K.C, h->B,    \
-                                       h->motor_mask, ndof, n_cand, margin);                                      \
-    else launch_ex(solve_warp_kernel<CH, false, 0>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, ndof,    \
-                   n_cand, margin);                                                                               \
+    if (dbg) launch_ex(solve_warp_kernel<CH, true, 0, false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask, \
+                       ndof, n_cand, margin);                                                                     \
+    else if (h->solve_mode == 2) launch_ex(solve_warp_kernel<CH, false, 0, true>, persist_grid<CH>(h), 32, 0, st, \
+                                           pdl, h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);               \
+    else if (h->solve_mode == 1) launch_ex(solve_warp_kernel<CH, false, 14, false>, h->B.n, 32, 0, st, pdl,       \
+                                           h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);                    \
+    else launch_ex(solve_warp_kernel<CH, false, 0, false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask,   \
+                   ndof, n_cand, margin);                                                                         \
     if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
     SOLO_MARK(2);                                                                                                 \
     launch_ex(finish_kernel<CH>, grid, h->block, sm, st, pdl, h->K, h->B, epilogue, (int)(pdl && h->warm_finish), \
@@ -808,7 +837,8 @@ int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
       drop_graphs(h);
       return SOLO_OK;
     case SOLO_OPT_SOLVER_OCCUPANCY:
-      h->solve_hiocc = value < 0 ? h->B.n >= kHiOccEnvs : value != 0;
+      if (value > 2) return fail(h, SOLO_EINVAL, "SOLO_OPT_SOLVER_OCCUPANCY: 0, 1, 2 or -1");
+      h->solve_mode = value < 0 ? auto_solve_mode(h->B.n) : value;
       drop_graphs(h);
       return SOLO_OK;
     default:

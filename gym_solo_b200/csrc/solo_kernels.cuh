@@ -59,6 +59,7 @@ struct Buffers {
   float *yh;                 // [6 + kLegs * CH + 4][n]: solver output, then per-env solver statistics
   float *fac;                // [FactorLayout<CH>::kSize][n]
   float *kin;                // [n][KinLayout<CH>::kSize]: one contiguous record per env
+  int32_t *work;             // [2] zero between launches: the persistent solver's ticket counter and its check-out count
   int32_t n;
   int32_t obs_dim;
   int32_t snapshot_per_env;  // 0: one reset state for every env; 1: one per env (randomised start poses)

@@ -473,10 +473,12 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
 }
 
 // MINB: minimum resident blocks per SM the register allocation is held to.  0 = whatever the
-// solve needs (166 registers, 12 blocks per SM): fastest for one environment's chain, i.e. for
-// batches whose launch is its slowest environment.  14 = 128 registers (240 bytes of spills): 13
-// blocks per SM (shared memory then limits), the better trade once the launch is throughput bound (large batches).
-template <int CH, bool DBG, int MINB>
+// solve needs (168 registers, 12 blocks per SM): fastest for one environment's chain, i.e. for
+// batches whose launch is its slowest environment.  14 = 128 registers (spills): 13 blocks per SM
+// (shared memory then limits), the better trade for batches of a few waves.
+// PERSIST: the grid is ONE resident wave of warps that walk over the environments (below): for
+// batches of many waves, where the launch is throughput bound.
+template <int CH, bool DBG, int MINB, bool PERSIST>
 __global__ void __launch_bounds__(32, MINB)
 solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, const uint32_t motor_mask,
                   const int ndof_total, const int n_cand, const float margin) {
@@ -487,8 +489,19 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   constexpr unsigned FULL = 0xffffffffu;
   __shared__ __align__(16) WarpSolveSmem<CH> sm;
   const int lane = threadIdx.x;
-  const int64_t env = blockIdx.x;
-  const long long t_begin = clock64();
+  // PERSIST: the grid is one wave of warps, each of which walks over environments: its own block
+  // index, that plus the grid size, then whatever the launch's counter hands out (B.work[0]; drawn
+  // one environment ahead, so the atomic's latency is off the path).  While an environment is
+  // solved the NEXT one's record is copied into the unused tail of the active-contact array with
+  // cp.async: a throughput-bound launch then pays neither a block launch nor an exposed memory
+  // latency per environment.  The order changes nothing in the results: environments are
+  // independent.
+  constexpr int kStageEntries = (KL::kSize + AL::kSize - 1) / AL::kSize;
+  constexpr int kStageAt = kMaxContacts - kStageEntries;   // first entry of the staging area
+  static_assert(KL::kSize % 4 == 0 && (AL::kSize * 4) % 16 == 0, "records are copied 16 bytes at a time");
+  int64_t env = blockIdx.x;
+  int64_t nxt = PERSIST ? (int64_t)blockIdx.x + gridDim.x : (int64_t)B.n;
+  bool staged = false;
 #ifdef SOLO_TIMELINE
   unsigned tl_begin;
   asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(tl_begin));
@@ -499,114 +512,153 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   cudaGridDependencySynchronize();
   cudaTriggerProgrammaticLaunchCompletion();
 
-  // ---- the environment's record -> smem ----
-  {
-    const float4 *src = reinterpret_cast<const float4 *>(B.kin + env * KL::kSize);
-    float4 *dst = reinterpret_cast<float4 *>(sm.kin);
-    for (int i = lane; i < KL::kSize / 4; i += 32) dst[i] = __ldcg(src + i);
-  }
-  __syncwarp();
-
-  // ---- contact detection: support points inside the breaking threshold, in
-  // Bullet's order (by body, then by support point), capped at max_contacts ----
-  int nc = 0;
-  {
-    constexpr int kRounds = kMaxCand / 32;
-    uint32_t hits[kRounds];
-#pragma unroll
-    for (int i = 0; i < kRounds; i++) {
-      const int c = lane + 32 * i;
-      bool hit = false;
-      if (c < n_cand) hit = cand_distance<CH>(sm.kin, load_cand(B.cand_tab, c), margin) < C.breaking;
-      hits[i] = __ballot_sync(FULL, hit);
+  // start the copy of the next environment's record into the staging area (if there is one and
+  // the area is free)
+  auto prefetch_next = [&](const bool stage_free) {
+    staged = stage_free && nxt < B.n;
+    if (staged) {
+      const float4 *src = reinterpret_cast<const float4 *>(B.kin + nxt * KL::kSize);
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&sm.ent[kStageAt][0]);
+      for (int i = lane; i < KL::kSize / 4; i += 32)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + i) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    int before = 0;
-#pragma unroll
-    for (int i = 0; i < kRounds; i++) {
-      const int rank = before + __popc(hits[i] & ((1u << lane) - 1u));
-      SOLO_CHECK(C.max_contacts <= kMaxContacts);
-      if (((hits[i] >> lane) & 1u) && rank < C.max_contacts) sm.list[rank] = lane + 32 * i;
-      before += __popc(hits[i]);
+  };
+  for (; env < B.n;) {
+    const long long t_begin = clock64();
+    int ticket = 0;
+    if (PERSIST && lane == 0) ticket = atomicAdd(B.work, 1);   // read at the end of this environment
+
+    // ---- the environment's record -> smem ----
+    if (PERSIST && staged) {
+      asm volatile("cp.async.wait_all;" ::: "memory");
+      __syncwarp();
+      const float4 *src = reinterpret_cast<const float4 *>(&sm.ent[kStageAt][0]);
+      float4 *dst = reinterpret_cast<float4 *>(sm.kin);
+      for (int i = lane; i < KL::kSize / 4; i += 32) dst[i] = src[i];
+    } else {
+      const float4 *src = reinterpret_cast<const float4 *>(B.kin + env * KL::kSize);
+      float4 *dst = reinterpret_cast<float4 *>(sm.kin);
+      for (int i = lane; i < KL::kSize / 4; i += 32) dst[i] = __ldcg(src + i);
     }
-    nc = min(before, C.max_contacts);
-  }
-  __syncwarp();
+    __syncwarp();
+    // ---- contact detection: support points inside the breaking threshold, in
+    // Bullet's order (by body, then by support point), capped at max_contacts ----
+    int nc = 0;
+    {
+      constexpr int kRounds = kMaxCand / 32;
+      uint32_t hits[kRounds];
+#pragma unroll
+      for (int i = 0; i < kRounds; i++) {
+        const int c = lane + 32 * i;
+        bool hit = false;
+        if (c < n_cand) hit = cand_distance<CH>(sm.kin, load_cand(B.cand_tab, c), margin) < C.breaking;
+        hits[i] = __ballot_sync(FULL, hit);
+      }
+      int before = 0;
+#pragma unroll
+      for (int i = 0; i < kRounds; i++) {
+        const int rank = before + __popc(hits[i] & ((1u << lane) - 1u));
+        SOLO_CHECK(C.max_contacts <= kMaxContacts);
+        if (((hits[i] >> lane) & 1u) && rank < C.max_contacts) sm.list[rank] = lane + 32 * i;
+        before += __popc(hits[i]);
+      }
+      nc = min(before, C.max_contacts);
+    }
+    __syncwarp();
+    // the solve touches entries [0, nc) only: the staging area is free unless the environment has
+    // more contacts than that (rare; the next record is then loaded the plain way)
+    if (PERSIST) prefetch_next(nc <= kStageAt);
 
-  float y[W], mlam[kLegs * CH];
-  int it = 0, n_active = 0;
-  const uint32_t lim = __float_as_uint(sm.kin[KL::kLim]);   // live joint-limit rows (setup)
-  if (lane < kLegs * CH) sm.llam[lane] = 0.f;
-  __syncwarp();
-  if (motor_mask != 0 || nc > 0 || lim != 0) {
-    const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
-    if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
-    else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
-  } else {
+    float y[W], mlam[kLegs * CH];
+    int it = 0, n_active = 0;
+    const uint32_t lim = __float_as_uint(sm.kin[KL::kLim]);   // live joint-limit rows (setup)
+    if (lane < kLegs * CH) sm.llam[lane] = 0.f;
+    __syncwarp();
+    if (motor_mask != 0 || nc > 0 || lim != 0) {
+      const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
+      if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+      else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+    } else {
 #pragma unroll
-    for (int a = 0; a < W; a++) y[a] = 0.f;
+      for (int a = 0; a < W; a++) y[a] = 0.f;
 #pragma unroll
-    for (int j = 0; j < kLegs * CH; j++) mlam[j] = 0.f;
-  }
+      for (int j = 0; j < kLegs * CH; j++) mlam[j] = 0.f;
+    }
 
-  // ---- outputs ----
-  {
-    // yh is warp-uniform: lane a writes entry a
-    float v = 0.f;
+    // ---- outputs ----
+    {
+      // yh is warp-uniform: lane a writes entry a
+      float v = 0.f;
 #pragma unroll
-    for (int a = 0; a < W; a++)
-      if (lane == a) v = y[a];
-    if (lane < W) B.yh[(int64_t)lane * B.n + env] = v;
-  }
-  if (lane == 0) {
-    // per-env solver statistics: iterations, contacts, contacts that carried an
-    // impulse, SM cycles spent in the solve
-    float *st = B.yh + (int64_t)W * B.n + env;
-    st[0] = (float)it; st[(int64_t)B.n] = (float)nc; st[2 * (int64_t)B.n] = (float)n_active;
-    st[3 * (int64_t)B.n] = (float)(clock64() - t_begin);
+      for (int a = 0; a < W; a++)
+        if (lane == a) v = y[a];
+      if (lane < W) B.yh[(int64_t)lane * B.n + env] = v;
+    }
+    if (lane == 0) {
+      // per-env solver statistics: iterations, contacts, contacts that carried an
+      // impulse, SM cycles spent in the solve
+      float *st = B.yh + (int64_t)W * B.n + env;
+      st[0] = (float)it; st[(int64_t)B.n] = (float)nc; st[2 * (int64_t)B.n] = (float)n_active;
+      st[3 * (int64_t)B.n] = (float)(clock64() - t_begin);
 #ifdef SOLO_SECTION_PROBE
-    // probe build (tools/solver_sections.py): the contact-count rows carry cycles in the normal rows
-    // (low 3 decimal digits: active contacts) and in the friction pairs (low 3 digits: screens / 10)
-    if (it > 0) {
-      st[0] = (float)(it + 100 * (sm.probe[3] / 100));
-      st[(int64_t)B.n] = (float)sm.probe[0];
-      st[2 * (int64_t)B.n] = (float)sm.probe[1];
-    }
+      // probe build (tools/solver_sections.py): the contact-count rows carry cycles in the normal rows
+      // (low 3 decimal digits: active contacts) and in the friction pairs (low 3 digits: screens / 10)
+      if (it > 0) {
+        st[0] = (float)(it + 100 * (sm.probe[3] / 100));
+        st[(int64_t)B.n] = (float)sm.probe[0];
+        st[2 * (int64_t)B.n] = (float)sm.probe[1];
+      }
 #endif
 #ifdef SOLO_TIMELINE
-    {
-      // probe build (tools/solver_timeline.py): the contact-count rows carry the block's start
-      // and end time in ns (low 32 bits of %globaltimer) instead
-      unsigned tl_end;
-      asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(tl_end));
-      st[(int64_t)B.n] = __uint_as_float(tl_begin);
-      st[2 * (int64_t)B.n] = __uint_as_float(tl_end);
-    }
-#endif
-  }
-  if (DBG) {
-    __syncwarp();
-    if (B.dbg_normal_force) {
-      for (int c = lane; c < n_cand; c += 32) B.dbg_normal_force[(int64_t)c * B.n + env] = 0.f;
-      __syncwarp();
-      for (int k = lane; k < n_active; k += 32) {
-        const float *e = &sm.ent[k][0];
-        const int cand = __float_as_int(e[AL::kMeta + 6]);
-        B.dbg_normal_force[(int64_t)cand * B.n + env] = e[AL::kMeta] / e[W + 1] * C.inv_dt;
+      {
+        // probe build (tools/solver_timeline.py): the contact-count rows carry the block's start
+        // and end time in ns (low 32 bits of %globaltimer) instead
+        unsigned tl_end;
+        asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(tl_end));
+        st[(int64_t)B.n] = __uint_as_float(tl_begin);
+        st[2 * (int64_t)B.n] = __uint_as_float(tl_end);
       }
+#endif
     }
-    if (B.dbg_motor_torque && lane == 0) {
-      // dof order == (leg, joint) order with inactive slots skipped
-      if (motor_mask == 0)
-        for (int k = 0; k < ndof_total; k++) B.dbg_motor_torque[(int64_t)k * B.n + env] = 0.f;
-      int d = 0;
-#pragma unroll
-      for (int j = 0; j < kLegs * CH; j++) {
-        if ((motor_mask >> j) & 1u) {
-          if (d < ndof_total)
-            B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * sm.kin[KL::kMotor + j * RL::kRow + RL::kIs] * C.inv_dt;
-          d++;
+    if (DBG) {
+      __syncwarp();
+      if (B.dbg_normal_force) {
+        for (int c = lane; c < n_cand; c += 32) B.dbg_normal_force[(int64_t)c * B.n + env] = 0.f;
+        __syncwarp();
+        for (int k = lane; k < n_active; k += 32) {
+          const float *e = &sm.ent[k][0];
+          const int cand = __float_as_int(e[AL::kMeta + 6]);
+          B.dbg_normal_force[(int64_t)cand * B.n + env] = e[AL::kMeta] / e[W + 1] * C.inv_dt;
         }
       }
+      if (B.dbg_motor_torque && lane == 0) {
+        // dof order == (leg, joint) order with inactive slots skipped
+        if (motor_mask == 0)
+          for (int k = 0; k < ndof_total; k++) B.dbg_motor_torque[(int64_t)k * B.n + env] = 0.f;
+        int d = 0;
+#pragma unroll
+        for (int j = 0; j < kLegs * CH; j++) {
+          if ((motor_mask >> j) & 1u) {
+            if (d < ndof_total)
+              B.dbg_motor_torque[(int64_t)d * B.n + env] = mlam[j] * sm.kin[KL::kMotor + j * RL::kRow + RL::kIs] * C.inv_dt;
+            d++;
+          }
+        }
+      }
+    }
+    if (!PERSIST) break;
+    // ---- next environment ----
+    __syncwarp();
+    env = nxt;
+    nxt = 2 * (int64_t)gridDim.x + __shfl_sync(FULL, ticket, 0);
+  }
+  if (PERSIST && lane == 0) {
+    // the last warp of the launch leaves the counters at zero for the next one: every warp's
+    // tickets are drawn before it checks out (work[1] wraps to 0 at the grid size by itself)
+    __threadfence();
+    if (atomicInc(reinterpret_cast<unsigned *>(B.work) + 1, gridDim.x - 1) == gridDim.x - 1) {
+      B.work[0] = 0;
     }
   }
 }

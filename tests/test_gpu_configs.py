@@ -469,6 +469,33 @@ def test_step_host_matches_device_step():
   a_env.close(); b_env.close()
 
 
+def test_solver_builds_give_the_same_bits():
+  """SOLO_OPT_SOLVER_OCCUPANCY: one block per environment (168 / 128 registers) and the persistent
+  build (one resident wave of warps drawing environments from a counter, next record prefetched
+  into the tail of the contact array) are the same arithmetic: identical states, observations and
+  solver statistics, launch after launch (the persistent build's counters must come back to zero).
+  2500 environments: more than one wave, so tickets and staging are exercised."""
+  from gym_solo_b200 import _abi as abi
+  n = 2500
+  envs = [_env(n, False, 1000) for _ in range(3)]
+  for mode, e in enumerate(envs):
+    e.reset()
+    e.client.set_option(abi.OPT_SOLVER_OCCUPANCY, mode)
+  g = torch.Generator(device='cuda:0').manual_seed(77)
+  for k in range(12):
+    act = (torch.rand((n, 12), generator=g, device='cuda:0') * 2 - 1) * 2 * np.pi
+    outs = [e.step(act) for e in envs]
+    for mode in (1, 2):
+      assert torch.equal(outs[0][0], outs[mode][0]) and torch.equal(outs[0][1], outs[mode][1]), (k, mode)
+      assert torch.equal(envs[0].get_state(), envs[mode].get_state()), (k, mode)
+      a, b = envs[0].client.solver_stats()[:3], envs[mode].client.solver_stats()[:3]
+      assert torch.equal(a, b), (k, mode)        # iterations, contacts, active contacts per environment
+  with pytest.raises(Exception):
+    envs[0].client.set_option(abi.OPT_SOLVER_OCCUPANCY, 3)
+  for e in envs:
+    e.close()
+
+
 def test_step_on_a_side_stream_and_launch_count():
   """The step captured and replayed on a caller stream (torch.cuda.stream): same bits as the
   default stream; launch_count() counts the kernels of the replayed graphs."""

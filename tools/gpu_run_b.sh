@@ -1,4 +1,6 @@
 #!/bin/bash
 O=gpurun_out; mkdir -p $O
-python tools/solver_ab.py 4096 product build/variants/lib_out.so product build/variants/lib_out.so 2>&1 | tee $O/ab_out.txt
-python tools/solver_ab.py 65536 product build/variants/lib_out.so 2>&1 | tee -a $O/ab_out.txt
+timeout 1200 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
+python bench.py --steps 100 --warmup 10 --envs 65536 --no-cpu-baseline > $O/bench_65536.json 2>/dev/null; head -c 250 $O/bench_65536.json; echo
+python bench.py --config 4 --steps 60 --warmup 10 --no-cpu-baseline > $O/bench_c4_1gpu.json 2>/dev/null; head -c 250 $O/bench_c4_1gpu.json; echo
+python bench.py --config 3 --steps 100 --warmup 10 --no-cpu-baseline > $O/bench_c3_1gpu.json 2>/dev/null; head -c 250 $O/bench_c3_1gpu.json; echo
