@@ -55,10 +55,12 @@ def oracle_pool(model, config, n_states, n_api, seed, targets, stride=5, low=-2 
   return np.stack(out)
 
 
-def test_mmr_v4_model_single_step_parity():
-  """configs[3]: examples/solo8_mmr (solo8_URDF_v4.urdf): 10 dof, hind chains of 3."""
+@pytest.mark.parametrize('name', ['solo8_mmr_v4', 'solo8_urdf_v3'])
+def test_mmr_v4_model_single_step_parity(name):
+  """configs[3]: examples/solo8_mmr (solo8_URDF_v4.urdf): 10 dof, hind chains of 3; and the
+  v3 URDF the reference ships beside it (same topology, other inertias and meshes)."""
   n = 192
-  c, model, config = make_client(n, name='solo8_mmr_v4', dt=1.0 / 240.0)
+  c, model, config = make_client(n, name=name, dt=1.0 / 240.0)
   assert model.ndof == 10 and model.n_api == 10
   states = oracle_pool(model, config, n, 10, seed=11, targets=np.zeros(10))
   rng = np.random.RandomState(12)

@@ -1,2 +1,2 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -q -x -k "solver_builds" 2>&1 | tail -15
+timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -q -x -k "mmr_v4_model" 2>&1 | tail -15
