@@ -106,7 +106,7 @@ static int pick_block(int n_envs) {
 
 constexpr int kHiOccEnvs = 10240;   // measured crossover between 8192 (-1.4 %) and 12288 (+1.3 %) environments
 #ifndef SOLO_PERSIST_ENVS
-#define SOLO_PERSIST_ENVS 32768      // from here the persistent solver build (measured: even at 32768, -7 % at 65536)
+#define SOLO_PERSIST_ENVS 28672      // from here the persistent solver build (measured: +2 % at 24576, -3 % at 32768, -10 % at 65536)
 #endif
 static int auto_solve_mode(int n) { return n >= SOLO_PERSIST_ENVS ? 2 : n >= kHiOccEnvs ? 1 : 0; }
 

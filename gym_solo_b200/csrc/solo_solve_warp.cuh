@@ -62,16 +62,32 @@ struct ActiveLayout {
   static constexpr int kSize = kMeta + 8;            // 64 floats (CH 2), 76 (CH 3)
 };
 
-template <int CH>
+// TAB: the block keeps its own copy of the support-point table (persistent build: filled once per
+// warp, read by every environment it walks over; the L1 is all but gone to the shared-memory
+// carve-out, so the global table costs an L2 round trip twice per environment)
+template <int CH, bool TAB = false>
 struct WarpSolveSmem {
   float kin[KinLayout<CH>::kSize];                   // setup_kernel's record (motor rows first)
   float ent[kMaxContacts][ActiveLayout<CH>::kSize];  // active contacts, sorted by contact index
   int32_t list[kMaxContacts];                        // contact -> support point
   float llam[kLegs * CH];                            // scaled joint-limit impulses (rows are rare)
-#ifdef SOLO_SECTION_PROBE
+  float4 ctab[TAB ? kMaxCand : 1];                   // support point xyz, friction
+  uint8_t cbody[TAB ? kMaxCand : 4];                 // (leg + 1) << 4 | depth in the chain
+#if defined(SOLO_SECTION_PROBE) || defined(SOLO_PROLOGUE_PROBE)
   long long probe[4];                                // probe build: cycles in normal rows / friction pairs, screens
 #endif
 };
+
+template <int CH, bool TAB>
+__device__ __forceinline__ Cand cand_at(const WarpSolveSmem<CH, TAB> &sm, const float *tab, const int c) {
+  if (!TAB) return load_cand(tab, c);
+  const float4 a = sm.ctab[c];
+  const int b = sm.cbody[c];
+  Cand k;
+  k.x = a.x; k.y = a.y; k.z = a.z; k.mu = a.w;
+  k.leg = (b >> 4) - 1; k.depth = b & 15;
+  return k;
+}
 
 // contact bitmasks: 32 bits when the env has <= 32 contacts (99.8 % of env-steps), else 64
 template <int NR> struct CMask;
@@ -158,8 +174,8 @@ __device__ __noinline__ void build_entry(float *e, const float *kin, const Confi
 
 // The solve proper.  NR = dense normal rows per lane (1: <= 32 contacts, 2: <= 64).
 // Returns iterations; y = yh, mlam = scaled motor impulses, *n_active = entries of sm.ent.
-template <int CH, int NR>
-__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH> &sm, const float margin,
+template <int CH, int NR, bool TAB>
+__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH, TAB> &sm, const float margin,
                                           const float *cand_tab, const float link_mu, const uint32_t motor_mask,
                                           const uint32_t lim, const int nc, const int lane, float (&y)[6 + kLegs * CH],
                                           float (&mlam)[kLegs * CH], int *n_active) {
@@ -179,7 +195,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
     const bool valid = c < nc;
     const int cand = valid ? sm.list[c] : 0;
     SOLO_CHECK(cand >= 0 && cand < kMaxCand && nc <= kMaxContacts && nc <= 32 * NR);
-    const Cand k = load_cand(cand_tab, cand);
+    const Cand k = cand_at(sm, cand_tab, cand);
     float row[1][RL::kRow];
     build_contact_rows<CH, 1>(sm.kin, C, margin, k, cand, row);
 #pragma unroll
@@ -256,6 +272,9 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
       budget -= fabsf(d);
     }
   };
+#ifdef SOLO_PROLOGUE_PROBE
+  if (lane == 0) sm.probe[2] = clock64();   // rows built: the iterations start
+#endif
   for (; it < C.iters;) {
     float res = 0.f;
     PROBE_T();
@@ -487,7 +506,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   typedef ActiveLayout<CH> AL;
   constexpr int W = 6 + kLegs * CH;   // dense width
   constexpr unsigned FULL = 0xffffffffu;
-  __shared__ __align__(16) WarpSolveSmem<CH> sm;
+  __shared__ __align__(16) WarpSolveSmem<CH, PERSIST> sm;
   const int lane = threadIdx.x;
   // PERSIST: the grid is one wave of warps, each of which walks over environments: its own block
   // index, that plus the grid size, then whatever the launch's counter hands out (B.work[0]; drawn
@@ -507,6 +526,15 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(tl_begin));
 #endif
 
+  if (PERSIST) {
+    // the warp's copy of the support-point table (not written by setup_legpar_kernel: in front of the wait on it)
+    for (int c = lane; c < kMaxCand; c += 32) {
+      const Cand k = load_cand(B.cand_tab, c);
+      sm.ctab[c] = make_float4(k.x, k.y, k.z, k.mu);
+      sm.cbody[c] = (uint8_t)(((k.leg + 1) << 4) | (k.depth & 15));
+    }
+    __syncwarp();
+  }
   // programmatic dependent of setup_legpar_kernel: wait for its records, then let the finish
   // kernel's blocks be scheduled behind the last solver block
   cudaGridDependencySynchronize();
@@ -526,10 +554,12 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   };
   for (; env < B.n;) {
     const long long t_begin = clock64();
-    int ticket = 0;
-    if (PERSIST && lane == 0) ticket = atomicAdd(B.work, 1);   // read at the end of this environment
 
     // ---- the environment's record -> smem ----
+#ifdef SOLO_PROLOGUE_PROBE
+    const bool was_staged = PERSIST && staged;
+    const long long t_wait0 = clock64();
+#endif
     if (PERSIST && staged) {
       asm volatile("cp.async.wait_all;" ::: "memory");
       __syncwarp();
@@ -542,6 +572,13 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
       for (int i = lane; i < KL::kSize / 4; i += 32) dst[i] = __ldcg(src + i);
     }
     __syncwarp();
+#ifdef SOLO_PROLOGUE_PROBE
+    if (lane == 0) { sm.probe[0] = clock64(); sm.probe[2] = 0; }   // record in shared memory
+#endif
+    // the ticket for the environment after next; read at the end of this one.  Drawn BEHIND the wait
+    // on the staged record: cp.async.wait_all waits on the scoreboard the atomic's return sits on too
+    int ticket = 0;
+    if (PERSIST && lane == 0) ticket = atomicAdd(B.work, 1);
     // ---- contact detection: support points inside the breaking threshold, in
     // Bullet's order (by body, then by support point), capped at max_contacts ----
     int nc = 0;
@@ -552,7 +589,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
       for (int i = 0; i < kRounds; i++) {
         const int c = lane + 32 * i;
         bool hit = false;
-        if (c < n_cand) hit = cand_distance<CH>(sm.kin, load_cand(B.cand_tab, c), margin) < C.breaking;
+        if (c < n_cand) hit = cand_distance<CH>(sm.kin, cand_at(sm, B.cand_tab, c), margin) < C.breaking;
         hits[i] = __ballot_sync(FULL, hit);
       }
       int before = 0;
@@ -566,6 +603,9 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
       nc = min(before, C.max_contacts);
     }
     __syncwarp();
+#ifdef SOLO_PROLOGUE_PROBE
+    if (lane == 0) sm.probe[1] = clock64();   // contacts listed
+#endif
     // the solve touches entries [0, nc) only: the staging area is free unless the environment has
     // more contacts than that (rare; the next record is then loaded the plain way)
     if (PERSIST) prefetch_next(nc <= kStageAt);
@@ -577,8 +617,8 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     __syncwarp();
     if (motor_mask != 0 || nc > 0 || lim != 0) {
       const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
-      if (nc <= 32) it = warp_solve<CH, 1>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
-      else it = warp_solve<CH, 2>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+      if (nc <= 32) it = warp_solve<CH, 1, PERSIST>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+      else it = warp_solve<CH, 2, PERSIST>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
     } else {
 #pragma unroll
       for (int a = 0; a < W; a++) y[a] = 0.f;
@@ -586,6 +626,9 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
       for (int j = 0; j < kLegs * CH; j++) mlam[j] = 0.f;
     }
 
+#ifdef SOLO_PROLOGUE_PROBE
+    const long long t_solved = clock64();
+#endif
     // ---- outputs ----
     {
       // yh is warp-uniform: lane a writes entry a
@@ -601,6 +644,15 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
       float *st = B.yh + (int64_t)W * B.n + env;
       st[0] = (float)it; st[(int64_t)B.n] = (float)nc; st[2 * (int64_t)B.n] = (float)n_active;
       st[3 * (int64_t)B.n] = (float)(clock64() - t_begin);
+#ifdef SOLO_PROLOGUE_PROBE
+      // probe build (tools/solver_prologue.py): cycles until the record is in shared memory, from
+      // there until the contacts are listed, from there until the iterations start (0: no solve);
+      // row 3: the iterations themselves
+      st[0] = (float)(sm.probe[0] - t_begin) * (was_staged ? 1.f : -1.f);   // < 0: the record came the plain way
+      st[(int64_t)B.n] = (float)(sm.probe[1] - sm.probe[0]);
+      st[2 * (int64_t)B.n] = sm.probe[2] ? (float)(sm.probe[2] - sm.probe[1]) : 0.f;
+      st[3 * (int64_t)B.n] = sm.probe[2] ? (float)(t_solved - sm.probe[2]) : 0.f;
+#endif
 #ifdef SOLO_SECTION_PROBE
       // probe build (tools/solver_sections.py): the contact-count rows carry cycles in the normal rows
       // (low 3 decimal digits: active contacts) and in the friction pairs (low 3 digits: screens / 10)

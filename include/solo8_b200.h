@@ -243,7 +243,7 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  *                      1 = one block per environment, 128 registers / 13 blocks per SM (a few
  *                      waves), 2 = persistent: one resident wave of warps that draw environments
  *                      from a counter and prefetch the next record (many waves), -1 = by batch
- *                      size (default: 0 below 10240 environments, 2 from 24576).  Same results
+ *                      size (default: 0 below 10240 environments, 2 from 28672).  Same results
  *                      bit for bit.
  *  SOLO_OPT_FINISH_WARMUP  1 = finish_kernel, launched as a programmatic dependent of the solver,
  *                      runs one dry pass (no side effects) while the solver drains so that its

@@ -1,2 +1,6 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -q -x -k "mmr_v4_model" 2>&1 | tail -15
+O=gpurun_out; mkdir -p $O
+timeout 1200 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
+python bench.py --steps 100 --warmup 10 --envs 65536 --no-cpu-baseline > $O/bench_65536.json 2>/dev/null; head -c 250 $O/bench_65536.json; echo
+python bench.py --config 4 --steps 60 --warmup 10 --no-cpu-baseline > $O/bench_c4_1gpu.json 2>/dev/null; head -c 250 $O/bench_c4_1gpu.json; echo
+python tools/solver_ab.py 20480,24576 product@occ=1 product@occ=2 2>&1 | tee $O/ab_thr.txt
