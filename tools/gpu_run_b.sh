@@ -1,6 +1,8 @@
 #!/bin/bash
+# ncu captures of the solver at the throughput-bound sizes (persistent build)
 O=gpurun_out; mkdir -p $O
-timeout 1200 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
-python bench.py --steps 100 --warmup 10 --envs 65536 --no-cpu-baseline > $O/bench_65536.json 2>/dev/null; head -c 250 $O/bench_65536.json; echo
-python bench.py --config 4 --steps 60 --warmup 10 --no-cpu-baseline > $O/bench_c4_1gpu.json 2>/dev/null; head -c 250 $O/bench_c4_1gpu.json; echo
-python tools/solver_ab.py 20480,24576 product@occ=1 product@occ=2 2>&1 | tee $O/ab_thr.txt
+for n in 65536 32768; do
+  ncu --set full --clock-control none --import-source on -k regex:solve_warp_kernel --launch-skip 515 -c 1 -f -o $O/solve_warp_kernel_r2_$n \
+    python bench.py --steps 20 --warmup 3 --envs $n --no-cpu-baseline > /dev/null 2>&1
+done
+ls -la $O/*.ncu-rep
