@@ -471,14 +471,15 @@ def test_step_host_matches_device_step():
   a_env.close(); b_env.close()
 
 
-def test_solver_builds_give_the_same_bits():
+@pytest.mark.parametrize('n', [100, 2500])
+def test_solver_builds_give_the_same_bits(n):
   """SOLO_OPT_SOLVER_OCCUPANCY: one block per environment (168 / 128 registers) and the persistent
   build (one resident wave of warps drawing environments from a counter, next record prefetched
   into the tail of the contact array) are the same arithmetic: identical states, observations and
   solver statistics, launch after launch (the persistent build's counters must come back to zero).
-  2500 environments: more than one wave, so tickets and staging are exercised."""
+  2500 environments: more than one wave, so tickets and staging are exercised; 100: fewer
+  environments than resident warps."""
   from gym_solo_b200 import _abi as abi
-  n = 2500
   envs = [_env(n, False, 1000) for _ in range(3)]
   for mode, e in enumerate(envs):
     e.reset()
