@@ -558,7 +558,6 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     // ---- the environment's record -> smem ----
 #ifdef SOLO_PROLOGUE_PROBE
     const bool was_staged = PERSIST && staged;
-    const long long t_wait0 = clock64();
 #endif
     if (PERSIST && staged) {
       asm volatile("cp.async.wait_all;" ::: "memory");
