@@ -108,7 +108,12 @@ constexpr int kHiOccEnvs = 10240;   // measured crossover between 8192 (-1.4 %) 
 #ifndef SOLO_PERSIST_ENVS
 #define SOLO_PERSIST_ENVS 28672      // from here the persistent solver build (measured: +2 % at 24576, -3 % at 32768, -10 % at 65536)
 #endif
-static int auto_solve_mode(int n) { return n >= SOLO_PERSIST_ENVS ? 2 : n >= kHiOccEnvs ? 1 : 0; }
+// Register cap of the one-block-per-environment default build: chains of 3 joints (CH = 3) take 234
+// registers uncapped, which leaves 8 blocks per SM; held to 168 (10 blocks) the launch is 4 % shorter at
+// 4096 environments and 15 % at 16384 -- better than the 128-register build there (368 bytes of spills),
+// which CH = 3 therefore never picks.  The persistent build stays uncapped (measured: 3 % better).
+#define SOLO_MINB0(CH) ((CH) == 3 ? 10 : 0)
+static int auto_solve_mode(int n, int ch) { return n >= SOLO_PERSIST_ENVS ? 2 : (n >= kHiOccEnvs && ch == 2) ? 1 : 0; }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -314,7 +319,7 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
   // Up to a few waves of solver blocks the launch lasts as long as its slowest environment and the
   // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
   // and 13 instead of 12 resident warps per SM (128 registers; shared memory is then the limit) win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
-  h->solve_mode = auto_solve_mode(n_envs);
+  h->solve_mode = auto_solve_mode(n_envs, h->ch);
   h->persist_grid = 0;
   h->warm_finish = n_envs < kHiOccEnvs;
   h->motor_mask = 0;
@@ -551,7 +556,7 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
                                            pdl, h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);               \
     else if (h->solve_mode == 1) launch_ex(solve_warp_kernel<CH, false, 14, false>, h->B.n, 32, 0, st, pdl,       \
                                            h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);                    \
-    else launch_ex(solve_warp_kernel<CH, false, 0, false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask,   \
+    else launch_ex(solve_warp_kernel<CH, false, SOLO_MINB0(CH), false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask,   \
                    ndof, n_cand, margin);                                                                         \
     if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
     SOLO_MARK(2);                                                                                                 \
@@ -838,7 +843,7 @@ int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
       return SOLO_OK;
     case SOLO_OPT_SOLVER_OCCUPANCY:
       if (value > 2) return fail(h, SOLO_EINVAL, "SOLO_OPT_SOLVER_OCCUPANCY: 0, 1, 2 or -1");
-      h->solve_mode = value < 0 ? auto_solve_mode(h->B.n) : value;
+      h->solve_mode = value < 0 ? auto_solve_mode(h->B.n, h->ch) : value;
       drop_graphs(h);
       return SOLO_OK;
     default:
