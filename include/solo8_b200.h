@@ -243,8 +243,9 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  *                      1 = one block per environment, 128 registers / 13 blocks per SM (a few
  *                      waves), 2 = persistent: one resident wave of warps that draw environments
  *                      from a counter and prefetch the next record (many waves), -1 = by batch
- *                      size (default: 0 below 10240 environments, 2 from 28672).  Same results
- *                      bit for bit.
+ *                      size (default: 0 below 10240 environments, 2 from 28672; models with
+ *                      chains of 3 joints skip build 1 and hold build 0 to 168 registers).  Same
+ *                      results bit for bit.
  *  SOLO_OPT_FINISH_WARMUP  1 = finish_kernel, launched as a programmatic dependent of the solver,
  *                      runs one dry pass (no side effects) while the solver drains so that its
  *                      code and factors are warm for the pass that counts; 0 = off; -1 = by batch
