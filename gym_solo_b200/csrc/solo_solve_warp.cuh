@@ -65,7 +65,10 @@ struct ActiveLayout {
 // TAB: the block keeps its own copy of the support-point table (persistent build: filled once per
 // warp, read by every environment it walks over; the L1 is all but gone to the shared-memory
 // carve-out, so the global table costs an L2 round trip twice per environment)
-template <int CH, bool TAB = false>
+// STASH: every listed contact's support point is kept beside its index, so that a promotion
+// (on the dependent chain) does not go back to the global table.  Not in the 13-blocks-per-SM
+// build, which has no shared memory to spare.
+template <int CH, bool TAB = false, bool STASH = false>
 struct WarpSolveSmem {
   float kin[KinLayout<CH>::kSize];                   // setup_kernel's record (motor rows first)
   float ent[kMaxContacts][ActiveLayout<CH>::kSize];  // active contacts, sorted by contact index
@@ -73,20 +76,33 @@ struct WarpSolveSmem {
   float llam[kLegs * CH];                            // scaled joint-limit impulses (rows are rare)
   float4 ctab[TAB ? kMaxCand : 1];                   // support point xyz, friction
   uint8_t cbody[TAB ? kMaxCand : 4];                 // (leg + 1) << 4 | depth in the chain
+  float4 pstash[STASH ? kMaxContacts : 1];           // contact -> support point xyz, friction
+  uint8_t pbody[STASH ? kMaxContacts : 4];
 #if defined(SOLO_SECTION_PROBE) || defined(SOLO_PROLOGUE_PROBE)
   long long probe[4];                                // probe build: cycles in normal rows / friction pairs, screens
 #endif
 };
 
-template <int CH, bool TAB>
-__device__ __forceinline__ Cand cand_at(const WarpSolveSmem<CH, TAB> &sm, const float *tab, const int c) {
-  if (!TAB) return load_cand(tab, c);
-  const float4 a = sm.ctab[c];
-  const int b = sm.cbody[c];
+__device__ __forceinline__ Cand unpack_cand(const float4 a, const int b) {
   Cand k;
   k.x = a.x; k.y = a.y; k.z = a.z; k.mu = a.w;
   k.leg = (b >> 4) - 1; k.depth = b & 15;
   return k;
+}
+__device__ __forceinline__ uint8_t pack_body(const Cand &k) { return (uint8_t)(((k.leg + 1) << 4) | (k.depth & 15)); }
+
+// support point of listed contact v, from the nearest place that has it
+template <int CH, bool TAB, bool STASH>
+__device__ __forceinline__ Cand cand_of_contact(const WarpSolveSmem<CH, TAB, STASH> &sm, const float *tab, const int v) {
+  if (STASH) return unpack_cand(sm.pstash[v], sm.pbody[v]);
+  if (TAB) return unpack_cand(sm.ctab[sm.list[v]], sm.cbody[sm.list[v]]);
+  return load_cand(tab, sm.list[v]);
+}
+
+template <int CH, bool TAB, bool STASH>
+__device__ __forceinline__ Cand cand_at(const WarpSolveSmem<CH, TAB, STASH> &sm, const float *tab, const int c) {
+  if (!TAB) return load_cand(tab, c);
+  return unpack_cand(sm.ctab[c], sm.cbody[c]);
 }
 
 // contact bitmasks: 32 bits when the env has <= 32 contacts (99.8 % of env-steps), else 64
@@ -157,11 +173,10 @@ __device__ __forceinline__ void dense_axpy(float (&y)[W], const float (&r)[N], c
 // The owner lane of a promoted contact expands its three rows into entry `e`.
 template <int CH>
 __device__ __noinline__ void build_entry(float *e, const float *kin, const ConfigT<float> &C, const float margin,
-                                         const float *cand_tab, const int cand, const int contact, const float lam_n,
+                                         Cand k, const int cand, const int contact, const float lam_n,
                                          const float link_mu) {
   typedef RowLayout<CH> RL;
   typedef ActiveLayout<CH> AL;
-  Cand k = load_cand(cand_tab, cand);
   if (link_mu >= 0.f && k.leg >= 0) k.mu = link_mu;   // per-env friction of the non-base links
   float rows[3][RL::kRow];
   build_contact_rows<CH, 3>(kin, C, margin, k, cand, rows);
@@ -174,8 +189,8 @@ __device__ __noinline__ void build_entry(float *e, const float *kin, const Confi
 
 // The solve proper.  NR = dense normal rows per lane (1: <= 32 contacts, 2: <= 64).
 // Returns iterations; y = yh, mlam = scaled motor impulses, *n_active = entries of sm.ent.
-template <int CH, int NR, bool TAB>
-__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH, TAB> &sm, const float margin,
+template <int CH, int NR, bool TAB, bool STASH>
+__device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem<CH, TAB, STASH> &sm, const float margin,
                                           const float *cand_tab, const float link_mu, const uint32_t motor_mask,
                                           const uint32_t lim, const int nc, const int lane, float (&y)[6 + kLegs * CH],
                                           float (&mlam)[kLegs * CH], int *n_active) {
@@ -196,6 +211,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
     const int cand = valid ? sm.list[c] : 0;
     SOLO_CHECK(cand >= 0 && cand < kMaxCand && nc <= kMaxContacts && nc <= 32 * NR);
     const Cand k = cand_at(sm, cand_tab, cand);
+    if (STASH && valid) { sm.pstash[c] = make_float4(k.x, k.y, k.z, k.mu); sm.pbody[c] = pack_body(k); }
     float row[1][RL::kRow];
     build_contact_rows<CH, 1>(sm.kin, C, margin, k, cand, row);
 #pragma unroll
@@ -419,7 +435,7 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
           for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
         __syncwarp();
         // the owner lane builds the contact's three rows (the friction pair for the first time)
-        if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_tab, sm.list[v], v, dv, link_mu);
+        if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_of_contact(sm, cand_tab, v), sm.list[v], v, dv, link_mu);
         act |= MK::bit(v);
         n_act++;
         __syncwarp();
@@ -506,7 +522,8 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   typedef ActiveLayout<CH> AL;
   constexpr int W = 6 + kLegs * CH;   // dense width
   constexpr unsigned FULL = 0xffffffffu;
-  __shared__ __align__(16) WarpSolveSmem<CH, PERSIST> sm;
+  constexpr bool STASH = !PERSIST && MINB != 14;
+  __shared__ __align__(16) WarpSolveSmem<CH, PERSIST, STASH> sm;
   const int lane = threadIdx.x;
   // PERSIST: the grid is one wave of warps, each of which walks over environments: its own block
   // index, that plus the grid size, then whatever the launch's counter hands out (B.work[0]; drawn
@@ -531,7 +548,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     for (int c = lane; c < kMaxCand; c += 32) {
       const Cand k = load_cand(B.cand_tab, c);
       sm.ctab[c] = make_float4(k.x, k.y, k.z, k.mu);
-      sm.cbody[c] = (uint8_t)(((k.leg + 1) << 4) | (k.depth & 15));
+      sm.cbody[c] = pack_body(k);
     }
     __syncwarp();
   }
@@ -616,8 +633,8 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
     __syncwarp();
     if (motor_mask != 0 || nc > 0 || lim != 0) {
       const float link_mu = B.link_friction ? B.link_friction[env] : -1.f;   // < 0: the model's value
-      if (nc <= 32) it = warp_solve<CH, 1, PERSIST>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
-      else it = warp_solve<CH, 2, PERSIST>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+      if (nc <= 32) it = warp_solve<CH, 1, PERSIST, STASH>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
+      else it = warp_solve<CH, 2, PERSIST, STASH>(C, sm, margin, B.cand_tab, link_mu, motor_mask, lim, nc, lane, y, mlam, &n_active);
     } else {
 #pragma unroll
       for (int a = 0; a < W; a++) y[a] = 0.f;
