@@ -1,4 +1,6 @@
 #!/bin/bash
 O=gpurun_out; mkdir -p $O
-python bench.py --steps 100 --warmup 10 --envs 65536 --no-cpu-baseline > $O/bench_65536.json 2>/dev/null; head -c 250 $O/bench_65536.json; echo
-python bench.py --config 4 --steps 60 --warmup 10 --no-cpu-baseline > $O/bench_c4_1gpu.json 2>/dev/null; head -c 250 $O/bench_c4_1gpu.json; echo
+timeout 900 python -m pytest tests/test_gpu_configs.py tests/test_gpu_parity.py -m gpu -q -x 2>&1 | tail -3
+python tools/solver_ab.py 4096 build/variants/lib_base.so product build/variants/lib_base.so product 2>&1 | tee $O/ab_stash2.txt
+python tools/solver_ab.py 8192 cfg=2 build/variants/lib_base.so product build/variants/lib_base.so product 2>&1 | tee -a $O/ab_stash2.txt
+python tools/solver_ab.py 16384 cfg=3 build/variants/lib_base.so product 2>&1 | tee -a $O/ab_stash2.txt
