@@ -94,6 +94,7 @@ __device__ __forceinline__ uint8_t pack_body(const Cand &k) { return (uint8_t)((
 // support point of listed contact v, from the nearest place that has it
 template <int CH, bool TAB, bool STASH>
 __device__ __forceinline__ Cand cand_of_contact(const WarpSolveSmem<CH, TAB, STASH> &sm, const float *tab, const int v) {
+  SOLO_CHECK(v >= 0 && v < kMaxContacts && sm.list[v] >= 0 && sm.list[v] < kMaxCand);
   if (STASH) return unpack_cand(sm.pstash[v], sm.pbody[v]);
   if (TAB) return unpack_cand(sm.ctab[sm.list[v]], sm.cbody[sm.list[v]]);
   return load_cand(tab, sm.list[v]);
@@ -101,6 +102,7 @@ __device__ __forceinline__ Cand cand_of_contact(const WarpSolveSmem<CH, TAB, STA
 
 template <int CH, bool TAB, bool STASH>
 __device__ __forceinline__ Cand cand_at(const WarpSolveSmem<CH, TAB, STASH> &sm, const float *tab, const int c) {
+  SOLO_CHECK(c >= 0 && c < kMaxCand);
   if (!TAB) return load_cand(tab, c);
   return unpack_cand(sm.ctab[c], sm.cbody[c]);
 }
@@ -561,6 +563,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   // the area is free)
   auto prefetch_next = [&](const bool stage_free) {
     staged = stage_free && nxt < B.n;
+    SOLO_CHECK(nxt >= 0 && kStageAt >= 0 && (kMaxContacts - kStageAt) * AL::kSize >= KL::kSize);
     if (staged) {
       const float4 *src = reinterpret_cast<const float4 *>(B.kin + nxt * KL::kSize);
       const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&sm.ent[kStageAt][0]);

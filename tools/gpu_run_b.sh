@@ -1,3 +1,4 @@
 #!/bin/bash
 O=gpurun_out; mkdir -p $O
-python tools/solver_ab.py 4096,16384,65536 product build/variants/lib_setup2.so product build/variants/lib_setup2.so 2>&1 | tee $O/ab_setup2.txt
+for m in 0 1 2; do timeout 600 python tools/sanitizer_run.py build/variants/lib_checks.so $m 64 2>&1 | grep -v Warn | tail -8; done | tee $O/checks_run.txt
+timeout 600 python tools/sanitizer_run.py build/variants/lib_checks.so 2 4000 2>&1 | grep -v Warn | tail -8 | tee -a $O/checks_run.txt

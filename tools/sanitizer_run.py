@@ -1,6 +1,6 @@
 """Workload for a -DSOLO_CHECKS build of the library (every index into the solver warp's shared
 arrays checked; compute-sanitizer itself is closed on this pool, profiles/r2_compute_sanitizer_closed.txt):
-  python tools/sanitizer_run.py build/variants/lib_checks.so
+  python tools/sanitizer_run.py build/variants/lib_checks.so [solver build 0|1|2] [environments]
 64 environments, reset (the
 500 settle steps), 50 env.steps with random actions, then a belly-flop state with more than 32
 contacts so that the two-rows-per-lane instantiation warp_solve<CH, 2> and its promotions run,
@@ -18,9 +18,14 @@ if len(sys.argv) > 1:
   _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 import bench
 
+from gym_solo_b200 import _abi
 dev = torch.device('cuda', 0)
-n = 64
+# optional second argument: solver build (SOLO_OPT_SOLVER_OCCUPANCY 0 / 1 / 2) and batch size
+mode = int(sys.argv[2]) if len(sys.argv) > 2 else -1
+n = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 env = bench.make_env(1, n, dev)
+env.client.set_option(_abi.OPT_SOLVER_OCCUPANCY, mode)
+print('solver build', mode, 'environments', n)
 g = torch.Generator(device=dev).manual_seed(3)
 for k in range(50):
   o, r, d, _ = env.step((torch.rand((n, 12), generator=g, device=dev) * 2 - 1) * 2 * np.pi)
@@ -46,6 +51,7 @@ print('render', img.shape)
 env.close()
 # torque mode with joint-limit rows
 env = bench.make_env(4, n, dev)
+env.client.set_option(_abi.OPT_SOLVER_OCCUPANCY, mode)
 for k in range(60):
   env.step(torch.full((n, 12), 2.0, device=dev))
 torch.cuda.synchronize()
