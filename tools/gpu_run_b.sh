@@ -1,4 +1,5 @@
 #!/bin/bash
 O=gpurun_out; mkdir -p $O
-for m in 0 1 2; do timeout 600 python tools/sanitizer_run.py build/variants/lib_checks.so $m 64 2>&1 | grep -v Warn | tail -8; done | tee $O/checks_run.txt
-timeout 600 python tools/sanitizer_run.py build/variants/lib_checks.so 2 4000 2>&1 | grep -v Warn | tail -8 | tee -a $O/checks_run.txt
+python tools/solver_ab.py 8192 cfg=2 product product@zero_copy=0 2>&1 | tee $O/ab_zc.txt
+python tools/solver_ab.py 16384,65536 product product@zero_copy=0 2>&1 | tee -a $O/ab_zc.txt
+python tools/solver_ab.py 262144 cfg=4 product product@zero_copy=0 2>&1 | tee -a $O/ab_zc.txt
