@@ -172,21 +172,29 @@ __device__ __forceinline__ void dense_axpy(float (&y)[W], const float (&r)[N], c
   for (int a = 0; a < W; a++) y[a] = fmaf(r[a], d, y[a]);
 }
 
-// The owner lane of a promoted contact expands its three rows into entry `e`.
+// The three rows of a promoted contact, expanded into entry `e` by lanes 0, 1, 2 side by side (one
+// instruction stream, the direction is the lane: a third of the warp instructions of one lane building
+// all three; the promotion sits on the warp's dependent chain).  Called by the whole warp.
 template <int CH>
 __device__ __noinline__ void build_entry(float *e, const float *kin, const ConfigT<float> &C, const float margin,
                                          Cand k, const int cand, const int contact, const float lam_n,
-                                         const float link_mu) {
+                                         const float link_mu, const int lane) {
   typedef RowLayout<CH> RL;
   typedef ActiveLayout<CH> AL;
   if (link_mu >= 0.f && k.leg >= 0) k.mu = link_mu;   // per-env friction of the non-base links
-  float rows[3][RL::kRow];
-  build_contact_rows<CH, 3>(kin, C, margin, k, cand, rows);
-  store_dense<CH>(e, rows[0], k.leg, 2, AL::NW);
-  store_dense<CH>(e + AL::kFA, rows[1], k.leg, 4, AL::FW);
-  store_dense<CH>(e + AL::kFB, rows[2], k.leg, 4, AL::FW);
-  e[AL::kMeta] = lam_n; e[AL::kMeta + 1] = 0.f; e[AL::kMeta + 2] = 0.f; e[AL::kMeta + 3] = __int_as_float(contact);
-  e[AL::kMeta + 4] = 0.f; e[AL::kMeta + 5] = 0.f; e[AL::kMeta + 6] = __int_as_float(cand); e[AL::kMeta + 7] = 0.f;
+  const int dir = lane < 2 ? lane : 2;
+  float row[RL::kRow];
+  build_contact_row_dir<CH>(kin, C, margin, k, cand, dir, row);
+  const float is_n = __shfl_sync(0xffffffffu, row[RL::kIs], 0);
+  if (dir == 1) row[RL::kX] = k.mu * is_n;
+  if (lane < 3) {
+    if (dir == 0) store_dense<CH>(e, row, k.leg, 2, AL::NW);
+    else store_dense<CH>(e + (dir == 1 ? AL::kFA : AL::kFB), row, k.leg, 4, AL::FW);
+  }
+  if (lane == 0) {
+    e[AL::kMeta] = lam_n; e[AL::kMeta + 1] = 0.f; e[AL::kMeta + 2] = 0.f; e[AL::kMeta + 3] = __int_as_float(contact);
+    e[AL::kMeta + 4] = 0.f; e[AL::kMeta + 5] = 0.f; e[AL::kMeta + 6] = __int_as_float(cand); e[AL::kMeta + 7] = 0.f;
+  }
 }
 
 // The solve proper.  NR = dense normal rows per lane (1: <= 32 contacts, 2: <= 64).
@@ -436,8 +444,8 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
         for (int s = n_act - 1; s >= k; s--)
           for (int j = lane; j < AL::kSize; j += 32) sm.ent[s + 1][j] = sm.ent[s][j];
         __syncwarp();
-        // the owner lane builds the contact's three rows (the friction pair for the first time)
-        if (lane == (v & 31)) build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_of_contact(sm, cand_tab, v), sm.list[v], v, dv, link_mu);
+        // lanes 0-2 build the contact's three rows (the friction pair for the first time)
+        build_entry<CH>(&sm.ent[k][0], sm.kin, C, margin, cand_of_contact(sm, cand_tab, v), sm.list[v], v, dv, link_mu, lane);
         act |= MK::bit(v);
         n_act++;
         __syncwarp();
