@@ -30,8 +30,8 @@ struct SoloHandle_ {
   bool legpar;            // setup phase with one lane per (environment, leg): latency-bound batch sizes
   int block;              // threads per block of the one-thread-per-env kernels
   int persist_grid;       // grid of the persistent solver build: one resident wave of one-warp blocks
-  int solve_mode;         // solver build: 0 = one block per env, 168 registers; 1 = one block per env, 128 registers
-                          // (13 blocks per SM); 2 = persistent warps (SOLO_OPT_SOLVER_OCCUPANCY)
+  int solve_mode;         // solver build: 0 (and 1, kept as an alias) = one block per env; 2 = persistent warps
+                          // (SOLO_OPT_SOLVER_OCCUPANCY)
   bool warm_finish;       // finish_kernel runs a dry pass behind the solver (small batches: fetch bound)
   uint32_t motor_mask;    // live motor rows (0 in torque mode)
   bool program_set;
@@ -104,16 +104,15 @@ static int pick_block(int n_envs) {
   return 32;
 }
 
-constexpr int kHiOccEnvs = 10240;   // measured crossover between 8192 (-1.4 %) and 12288 (+1.3 %) environments
+constexpr int kHiOccEnvs = 10240;   // below this finish_kernel's dry warm-up pass pays (SOLO_OPT_FINISH_WARMUP)
 #ifndef SOLO_PERSIST_ENVS
 #define SOLO_PERSIST_ENVS 28672      // from here the persistent solver build (measured: +2 % at 24576, -3 % at 32768, -10 % at 65536)
 #endif
-// Register cap of the one-block-per-environment default build: chains of 3 joints (CH = 3) take 234
-// registers uncapped, which leaves 8 blocks per SM; held to 168 (10 blocks) the launch is 4 % shorter at
-// 4096 environments and 15 % at 16384 -- better than the 128-register build there (368 bytes of spills),
-// which CH = 3 therefore never picks.  The persistent build stays uncapped (measured: 3 % better).
+// Register cap of the one-block-per-environment build: chains of 3 joints (CH = 3) are held to 168
+// registers (10 blocks per SM; measured against uncapped and against 128 registers, profiles/README.md);
+// CH = 2 needs 127 and is limited by shared memory.  The persistent build stays uncapped.
 #define SOLO_MINB0(CH) ((CH) == 3 ? 10 : 0)
-static int auto_solve_mode(int n, int ch) { return n >= SOLO_PERSIST_ENVS ? 2 : (n >= kHiOccEnvs && ch == 2) ? 1 : 0; }
+static int auto_solve_mode(int n) { return n >= SOLO_PERSIST_ENVS ? 2 : 0; }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -316,10 +315,9 @@ int solo_create(const SoloModel *model, const SoloConfig *config, int32_t n_envs
 #endif
     if (h->legpar && h->block > 64) h->block = 64;   // 4 lanes per environment, 256-thread blocks
   }
-  // Up to a few waves of solver blocks the launch lasts as long as its slowest environment and the
-  // 166-register build is faster (4096 envs: 0.145 vs 0.151 ms); beyond, issue slots are the limit
-  // and 13 instead of 12 resident warps per SM (128 registers; shared memory is then the limit) win (16384: 0.285 -> 0.275 ms, 65536: 0.855 -> 0.787 ms)
-  h->solve_mode = auto_solve_mode(n_envs, h->ch);
+  // Up to a few waves of solver blocks the launch lasts as long as its slowest environment: one block per
+  // environment; with many waves issue slots are the limit and the persistent build wins (32768: -2 %, 65536: -9 %)
+  h->solve_mode = auto_solve_mode(n_envs);
   h->persist_grid = 0;
   h->warm_finish = n_envs < kHiOccEnvs;
   h->motor_mask = 0;
@@ -554,8 +552,6 @@ static int launch_physics(SoloHandle h, const float *actions_dev, int broadcast,
                        ndof, n_cand, margin);                                                                     \
     else if (h->solve_mode == 2) launch_ex(solve_warp_kernel<CH, false, 0, true>, persist_grid<CH>(h), 32, 0, st, \
                                            pdl, h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);               \
-    else if (h->solve_mode == 1) launch_ex(solve_warp_kernel<CH, false, 14, false>, h->B.n, 32, 0, st, pdl,       \
-                                           h->K.C, h->B, h->motor_mask, ndof, n_cand, margin);                    \
     else launch_ex(solve_warp_kernel<CH, false, SOLO_MINB0(CH), false>, h->B.n, 32, 0, st, pdl, h->K.C, h->B, h->motor_mask,   \
                    ndof, n_cand, margin);                                                                         \
     if ((rc = check_launch(h, "solve_warp_kernel"))) return rc;                                                   \
@@ -843,7 +839,7 @@ int solo_set_option(SoloHandle h, int32_t option, int32_t value) {
       return SOLO_OK;
     case SOLO_OPT_SOLVER_OCCUPANCY:
       if (value > 2) return fail(h, SOLO_EINVAL, "SOLO_OPT_SOLVER_OCCUPANCY: 0, 1, 2 or -1");
-      h->solve_mode = value < 0 ? auto_solve_mode(h->B.n, h->ch) : value;
+      h->solve_mode = value < 0 ? auto_solve_mode(h->B.n) : value;
       drop_graphs(h);
       return SOLO_OK;
     default:

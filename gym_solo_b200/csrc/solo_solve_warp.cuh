@@ -66,8 +66,7 @@ struct ActiveLayout {
 // warp, read by every environment it walks over; the L1 is all but gone to the shared-memory
 // carve-out, so the global table costs an L2 round trip twice per environment)
 // STASH: every listed contact's support point is kept beside its index, so that a promotion
-// (on the dependent chain) does not go back to the global table.  Not in the 13-blocks-per-SM
-// build, which has no shared memory to spare.
+// (on the dependent chain) does not go back to the global table.
 template <int CH, bool TAB = false, bool STASH = false>
 struct WarpSolveSmem {
   float kin[KinLayout<CH>::kSize];                   // setup_kernel's record (motor rows first)
@@ -517,10 +516,10 @@ __device__ __forceinline__ int warp_solve(const ConfigT<float> &C, WarpSolveSmem
   return it;
 }
 
-// MINB: minimum resident blocks per SM the register allocation is held to.  0 = whatever the
-// solve needs (168 registers, 12 blocks per SM): fastest for one environment's chain, i.e. for
-// batches whose launch is its slowest environment.  14 = 128 registers (spills): 13 blocks per SM
-// (shared memory then limits), the better trade for batches of a few waves.
+// MINB: minimum resident blocks per SM the register allocation is held to (0: none; the CH = 3
+// instantiation is held to 10 = 168 registers).  With the three rows of a promoted contact built by
+// three lanes side by side the CH = 2 solve takes 127 registers, so shared memory (16.9 KB a block)
+// is what limits residency: 13 one-warp blocks per SM.
 // PERSIST: the grid is ONE resident wave of warps that walk over the environments (below): for
 // batches of many waves, where the launch is throughput bound.
 template <int CH, bool DBG, int MINB, bool PERSIST>
@@ -532,7 +531,7 @@ solve_warp_kernel(const __grid_constant__ ConfigT<float> C, const Buffers B, con
   typedef ActiveLayout<CH> AL;
   constexpr int W = 6 + kLegs * CH;   // dense width
   constexpr unsigned FULL = 0xffffffffu;
-  constexpr bool STASH = !PERSIST && MINB != 14;
+  constexpr bool STASH = !PERSIST;
   __shared__ __align__(16) WarpSolveSmem<CH, PERSIST, STASH> sm;
   const int lane = threadIdx.x;
   // PERSIST: the grid is one wave of warps, each of which walks over environments: its own block

@@ -239,13 +239,12 @@ int solo_step_host(SoloHandle h, const float *actions_host, float action_scale,
  *                      set of output buffers instead of 3 x num_substeps launches
  *  SOLO_OPT_ZERO_COPY  solo_step_host on page-locked buffers without staging copies
  *  SOLO_OPT_SOLVER_OCCUPANCY  which build of the solver kernel runs: 0 = one block per
- *                      environment, 168 registers / 12 blocks per SM (latency: small batches),
- *                      1 = one block per environment, 128 registers / 13 blocks per SM (a few
- *                      waves), 2 = persistent: one resident wave of warps that draw environments
- *                      from a counter and prefetch the next record (many waves), -1 = by batch
- *                      size (default: 0 below 10240 environments, 2 from 28672; models with
- *                      chains of 3 joints skip build 1 and hold build 0 to 168 registers).  Same
- *                      results bit for bit.
+ *                      environment (latency: the launch is its slowest environment), 2 =
+ *                      persistent: one resident wave of warps that draw environments from a
+ *                      counter and prefetch the next record (many waves), -1 = by batch size
+ *                      (default: 2 from 28672 environments); 1 is accepted and means 0 (it used
+ *                      to select a 128-register build that no longer differs).  Same results
+ *                      bit for bit.
  *  SOLO_OPT_FINISH_WARMUP  1 = finish_kernel, launched as a programmatic dependent of the solver,
  *                      runs one dry pass (no side effects) while the solver drains so that its
  *                      code and factors are warm for the pass that counts; 0 = off; -1 = by batch
