@@ -178,7 +178,10 @@ int solo_set_program(SoloHandle h, const SoloProgram *program);
 int solo_obs_dim(SoloHandle h);
 /* Bytes of solver scratch the caller must bind (256-byte aligned): the
  * per-environment records setup leaves for the solver warp, mass-matrix
- * factors, solver output and the support-point table of one step. */
+ * factors, solver output and the support-point table of one step, and the
+ * persistent solver's two work counters.  solo_bind fills the table and zeroes
+ * the counters; between calls the scratch belongs to the library (the counters
+ * must still be zero at the next step) and to ONE stream at a time. */
 int64_t solo_scratch_bytes(SoloHandle h);
 
 /* Bind caller-owned device buffers.  state_dev: float[SOLO_STATE_DIM][n_envs];
